@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""bench.py — LZ4 frame compress + decompress throughput on B200 (BASELINE.json metric).
+
+A "step" is one pass of the hot path over one batch: compress the synthetic stream into ONE LZ4 frame
+and decompress that frame again.  `value` = uncompressed bytes through the round trip per second
+(U / (t_compress + t_decompress)), device-resident; `e2e` = the same through the host-buffer C-ABI
+calls (pinned host buffers, H2D + D2H inside the timed region).  compress / decompress GB/s are also
+reported separately, as are the rooflines of the two dominant kernels.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--size-mib M]
+N > 1: launched by torchrun, one rank per GPU, every rank its own stream (weak scaling, no collective on
+the data path: blocks are independent).
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "lz4f_roundtrip_uncompressed_GBps"
+UNIT = "GB/s"
+WORKLOAD = "config2: 1 GiB synthetic log-like stream (tools/b2gen.c, splitmix64 seed 0x10C5), 4 MB independent blocks, compress + decompress"
+
+
+def load_gen():
+    path = os.path.join(ROOT, "tools", "libb2gen.so")
+    if not os.path.exists(path):
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", path, os.path.join(ROOT, "tools", "b2gen.c")], check=True)
+    lib = C.CDLL(path)
+    lib.b2gen_loglike.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
+    lib.b2gen_loglike.restype = None
+    return lib
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+        sm, mx, reasons = [], 0.0, set()
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx = max(mx, float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def ref_lib():
+    path = os.path.join(ROOT, "oracle", "_ref", "libref.so")
+    if not os.path.exists(path):
+        if os.path.isdir("/root/reference/lz4/lib"):
+            subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "ref"], check=True, capture_output=True)
+        else:
+            return None
+    lib = C.CDLL(path)
+    sz = C.c_size_t
+    lib.ref_conduit_compress.restype = sz
+    lib.ref_conduit_compress.argtypes = [C.c_void_p, sz, C.c_void_p, sz, sz, sz]
+    lib.ref_conduit_decompress.restype = sz
+    lib.ref_conduit_decompress.argtypes = [C.c_void_p, sz, C.c_void_p, sz, sz, C.POINTER(sz)]
+    return lib
+
+
+def ref_roundtrip(lib, src_ptr, n, threads):
+    """The reference's CPU conduit (oracle/_ref: unmodified lz4 library + replay of Conduit.hsc's call
+    sequence) over `threads` independent slices, one OS thread each (ctypes releases the GIL).
+    Returns (t_compress, t_decompress, compressed_bytes)."""
+    import numpy as np
+    per = (n + threads - 1) // threads
+    slices = [(i * per, min(per, n - i * per)) for i in range(threads) if i * per < n]
+    comp = [np.empty(ln + ln // 100 + 200000, np.uint8) for _, ln in slices]
+    back = [np.empty(ln + 64, np.uint8) for _, ln in slices]
+    csz = [0] * len(slices)
+    ok = [True] * len(slices)
+
+    def run(fn):
+        ts = [threading.Thread(target=fn, args=(i,)) for i in range(len(slices))]
+        t0 = time.perf_counter()
+        for t in ts: t.start()
+        for t in ts: t.join()
+        return time.perf_counter() - t0
+
+    def do_c(i):
+        off, ln = slices[i]
+        csz[i] = lib.ref_conduit_compress(src_ptr + off, ln, comp[i].ctypes.data, comp[i].size, 32768, 0)
+
+    def do_d(i):
+        off, ln = slices[i]
+        consumed = C.c_size_t(0)
+        r = lib.ref_conduit_decompress(comp[i].ctypes.data, csz[i], back[i].ctypes.data, back[i].size, 32768, C.byref(consumed))
+        ok[i] = (r == ln)
+
+    tc = run(do_c)
+    td = run(do_d)
+    assert all(ok) and all(c < (1 << 62) for c in csz), "reference round trip failed"
+    return tc, td, sum(csz)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    lib = ref_lib()
+    import numpy as np
+    gen = load_gen()
+    n = args.size_mib << 20
+    threads = os.cpu_count() or 1
+    sample = min(n, max(64 << 20, (threads * 48) << 20))          # bounded: ~48 MiB per thread, <= the workload
+    buf = np.empty(sample, np.uint8)
+    gen.b2gen_loglike(buf.ctypes.data, sample, 0x10C5)
+    if lib is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref.so not built and /root/reference absent"}))
+        return 0
+    for _ in range(args.warmup):
+        ref_roundtrip(lib, buf.ctypes.data, min(sample, 64 << 20), threads)
+    t0 = time.perf_counter()
+    tcs = tds = 0.0
+    csize = 0
+    for _ in range(args.steps):
+        tc, td, csize = ref_roundtrip(lib, buf.ctypes.data, sample, threads)
+        tcs += tc; tds += td
+    wall = time.perf_counter() - t0
+    val = sample * args.steps / (tcs + tds) / 1e9
+    line = {"metric": METRIC, "value": val, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * (tcs + tds) / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": f"first {sample >> 20} MiB of the stream per step, {threads} slices"},
+            "compress_GBps": sample * args.steps / tcs / 1e9, "decompress_GBps": sample * args.steps / tds / 1e9,
+            "ratio": sample / csize,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "reference",
+                             "sample": f"{sample >> 20} MiB log-like, reference conduit replay (linked 64 KB blocks), {threads} threads on independent slices"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "wall_s": wall}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--size-mib", type=int, default=1024)
+    ap.add_argument("--sub-log2", type=int, default=18)
+    ap.add_argument("--no-index", action="store_true", help="plain frames (drop-in default) instead of seekable ones")
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        print("bench.py: no CUDA device — this benchmark has no CPU path", file=sys.stderr)
+        return 2
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    pkg = importlib.import_module("lz4-frame-conduit_b200")
+    gen = load_gen()
+    n = args.size_mib << 20
+    index = 0 if args.no_index else 1
+    codec = pkg.Codec(local, block_size_id=7, sub_block_log2=args.sub_log2, write_index=index, use_index=1)
+
+    # synthetic input: every rank its own stream (weak scaling), generated on the host, moved to HBM once
+    host_in = torch.empty(n, dtype=torch.uint8).pin_memory()
+    gen.b2gen_loglike(host_in.data_ptr(), n, 0x10C5 + rank)
+    d_in = host_in.cuda()
+    cap = pkg.compress_bound(n, codec.prefs)
+    d_comp = torch.empty(cap, dtype=torch.uint8, device="cuda")
+    d_back = torch.empty(n, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        c = codec.compress_device(d_in.data_ptr(), n, d_comp.data_ptr(), cap)
+        sc = codec.stats()
+        r, _ = codec.decompress_device(d_comp.data_ptr(), c, d_back.data_ptr(), n)
+        sd = codec.stats()
+        assert r == n
+        return c, sc, sd
+
+    for _ in range(args.warmup):
+        csize, _, _ = step_device()
+    assert torch.equal(d_back, d_in), "round trip is not bit-exact"
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    ev = {"c_total": 0.0, "c_main": 0.0, "d_total": 0.0, "d_main": 0.0, "launches": 0}
+    for _ in range(args.steps):
+        csize, sc, sd = step_device()
+        ev["c_total"] += sc.ms_total; ev["c_main"] += sc.ms_main
+        ev["d_total"] += sd.ms_total; ev["d_main"] += sd.ms_main
+        ev["launches"] += sc.kernel_launches + sd.kernel_launches
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    K = args.steps
+    dev_ms = (ev["c_total"] + ev["d_total"]) / K             # CUDA events on the codec's own stream
+    wall_ms = 1e3 * wall / K
+    t = torch.tensor([wall_ms, dev_ms, ev["c_total"] / K, ev["d_total"] / K], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    wall_ms, dev_ms, c_ms, d_ms = [float(x) for x in t.tolist()]
+
+    # ---- end to end through the host-buffer C ABI: pinned host in/out, copies inside the timed region
+    e2e = None
+    if not args.skip_e2e:
+        host_comp = torch.empty(cap, dtype=torch.uint8).pin_memory()
+        host_back = torch.empty(n, dtype=torch.uint8).pin_memory()
+
+        def step_host():
+            c = codec.compress_host_ptr(host_in.data_ptr(), n, host_comp.data_ptr(), cap)
+            r, _ = codec.decompress_host_ptr(host_comp.data_ptr(), c, host_back.data_ptr(), n)
+            assert r == n
+            return c
+        for _ in range(2):
+            step_host()
+        assert torch.equal(host_back, host_in)
+        barrier()
+        t1 = time.perf_counter()
+        ke = max(2, min(K, 5))
+        for _ in range(ke):
+            ce = step_host()
+        barrier()
+        e_ms = 1e3 * (time.perf_counter() - t1) / ke
+        te = torch.tensor([e_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e_ms = float(te.item())
+        e2e = {"value": world * n / (e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": n + ce,
+               "d2h_bytes_per_step": ce + n, "ms_per_step": e_ms, "steps": ke,
+               "api": "b2lz4_compress_host + b2lz4_decompress_host (pinned host buffers)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peaks()
+    alg = n + csize                                           # U + C per direction
+    rf_d = {"kernel": "decode_chains_kernel", "bound": "hbm", "achieved": alg / (ev["d_main"] / K * 1e-3) / 1e9,
+            "peak": peak, "unit": "GB/s", "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg, "avg_launch_ms": ev["d_main"] / K}
+    rf_c = {"kernel": "find_emit_kernel", "bound": "hbm", "achieved": alg / (ev["c_main"] / K * 1e-3) / 1e9,
+            "peak": peak, "unit": "GB/s", "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg, "avg_launch_ms": ev["c_main"] / K}
+    for r in (rf_d, rf_c):
+        r["frac"] = r["achieved"] / peak
+    dominant, other = (rf_c, rf_d) if ev["c_main"] >= ev["d_main"] else (rf_d, rf_c)
+
+    cpu = None
+    if not args.skip_cpu:
+        lib = ref_lib()
+        if lib is not None:
+            sample = min(n, 256 << 20)
+            tc, td, cs = ref_roundtrip(lib, host_in.data_ptr(), sample, 1)
+            cpu = {"value": sample / (tc + td) / 1e9, "unit": UNIT, "cores": 1, "kind": "reference",
+                   "sample": f"first {sample >> 20} MiB of the same stream, reference conduit replay (Conduit.hsc call sequence on the unmodified lz4 library), 1 thread",
+                   "compress_GBps": sample / tc / 1e9, "decompress_GBps": sample / td / 1e9, "ratio": sample / cs}
+
+    line = {"metric": METRIC, "value": world * n / (wall_ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": args.warmup, "ms_per_step": wall_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "bytes_per_gpu": n, "block_size": 4 << 20, "sub_block": 1 << args.sub_log2,
+                       "frame": "seekable (B2IX index frame appended)" if index else "plain (drop-in default)",
+                       "l2": "inputs larger than L2 (1 GiB stream vs 126 MB L2)", "parallelism": f"{world} independent streams, no collective"},
+            "compress_GBps": world * n / (c_ms * 1e-3) / 1e9, "decompress_GBps": world * n / (d_ms * 1e-3) / 1e9,
+            "device_ms_per_step": dev_ms, "ratio": n / csize, "compressed_bytes": csize,
+            "roofline": dominant, "roofline_other": other, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": ev["launches"], "clocks": clocks}
+    if cpu:
+        line["ratio_vs_reference_default"] = (n / csize) / cpu["ratio"]
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,103 @@
+/* b200lz4.h — C ABI of libb200lz4.so, the B200-native LZ4 frame codec behind the
+ * Codec.Compression.LZ4.Conduit compress / decompress conduits.
+ *
+ * Plain pointers and sizes only.  Every function that returns size_t follows the reference's error
+ * convention (lz4/lib/lz4frame.c:249-252): a value > (size_t)-B2LZ4_ERROR_maxCode is an error code;
+ * test with b2lz4_is_error(), name with b2lz4_error_name().  Codes 1..19 are numbered like
+ * LZ4F_LIST_ERRORS (lz4/lib/lz4frame.h:503-524).
+ *
+ * "Tier 2" (this header) is the batch interface the modified conduit calls; "Tier 1" (lz4frame.h in
+ * this directory) is the 12 LZ4F_* symbols the unmodified Conduit.hsc links against.  There is no CPU
+ * codec in this library: every compress/decompress entry point launches sm_100a kernels and fails
+ * with ERROR_cudaFailure when no device is usable.
+ */
+#ifndef B200LZ4_H
+#define B200LZ4_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2LZ4_ERROR_cudaFailure 20
+#define B2LZ4_ERROR_noEndMark   21   /* Conduit.hsc:689 "stream ended before EndMark" */
+#define B2LZ4_ERROR_maxCode     22
+
+typedef struct b2lz4_ctx b2lz4_ctx;
+
+/* Encoder preferences.  Mirrors the fields of the reference's Preferences / FrameInfo records
+ * (src/Codec/Compression/LZ4/CTypes.hsc:155-232; lz4/lib/lz4frame.h:169-192) that make sense for
+ * an independent-block GPU encoder, plus two knobs of this implementation. */
+typedef struct {
+    uint32_t block_size_id;     /* 0 = default (4 MB); 4..7 = 64 KB, 256 KB, 1 MB, 4 MB (lz4frame.h:115-124) */
+    uint32_t block_checksum;    /* XXH32 after every block (lz4frame.h:186-192 blockChecksumFlag) */
+    uint32_t content_checksum;  /* XXH32 of the whole content after the EndMark */
+    uint32_t content_size;      /* 1 = store the content size in the frame header (one-shot calls only) */
+    uint32_t sub_block_log2;    /* independent sub-block size inside a block: 0 = default (18 = 256 KB), 16..22 */
+    uint32_t write_index;       /* 1 = append the B2IX skippable index frame ("seekable" frame: block table + sub-block
+                                   entry points, lets the decoder run every sub-block in parallel).  Default 0: the
+                                   stock lz4 CLI skips skippable frames in files but fails on pipes (lz4io.c:1124-1133). */
+    uint32_t use_index;         /* decoder: 1 = trust-but-verify a trailing B2IX index frame */
+    uint32_t reserved;
+} b2lz4_prefs;
+
+typedef struct {                /* parsed frame header (replaces LZ4F_getFrameInfo, lz4frame.c:1246-1281) */
+    uint32_t block_size_id, block_independent, block_checksum, content_checksum;
+    uint32_t has_content_size, has_dict_id, dict_id, header_size;
+    uint64_t content_size;
+    uint64_t block_size;
+} b2lz4_frame_info;
+
+typedef struct {                /* what the last compress/decompress call on a context did */
+    uint32_t n_blocks, n_chains, indexed, kernel_launches;
+    float    ms_total;          /* first launch to last kernel, CUDA events on the context's stream */
+    float    ms_main;           /* the dominant kernel: match finder (compress) / sequence decoder (decompress) */
+    float    ms_aux;            /* everything else on the stream: scan, layout, gather, checksums */
+    float    ms_h2d, ms_d2h;    /* host-buffer entry points only */
+    uint64_t bytes_in, bytes_out;
+    uint32_t retries;           /* workspace growth / layout fallbacks taken */
+    uint32_t pad;
+} b2lz4_stats;
+
+/* ---- error helpers (replace LZ4F_isError / LZ4F_getErrorName, lz4frame.c:249-259) */
+unsigned    b2lz4_is_error(size_t code);
+const char* b2lz4_error_name(size_t code);
+const char* b2lz4_last_cuda_error(const b2lz4_ctx* ctx);
+
+/* ---- context (replaces LZ4F_create/freeCompressionContext + Decompression, lz4frame.c:536-563, 1065-1090).
+ * One context = one CUDA device + its streams + reusable workspaces.  Not thread-safe; independent
+ * contexts may be used concurrently from any OS thread. */
+size_t b2lz4_create(b2lz4_ctx** out, int device, const b2lz4_prefs* prefs /* NULL = defaults */);
+size_t b2lz4_destroy(b2lz4_ctx* ctx);                       /* NULL is a no-op */
+size_t b2lz4_set_prefs(b2lz4_ctx* ctx, const b2lz4_prefs* prefs);
+void   b2lz4_default_prefs(b2lz4_prefs* prefs);
+int    b2lz4_device_count(void);
+
+/* ---- sizes (replaces LZ4F_compressBound / LZ4F_compressFrameBound, lz4frame.c:324-349, 370-381) */
+size_t b2lz4_compress_bound(size_t n, const b2lz4_prefs* prefs);
+
+/* ---- host-only frame helpers: no GPU involved (replace lz4frame.c:663-701 and :1109-1198) */
+size_t b2lz4_frame_header_write(void* dst, size_t cap, const b2lz4_prefs* prefs, uint64_t content_size);
+size_t b2lz4_frame_header_parse(const void* src, size_t n, b2lz4_frame_info* info);   /* returns header size */
+
+/* ---- one LZ4 frame, buffers resident in device memory (config 2).  Return the frame size / the decoded
+ * size.  `consumed` (may be NULL) receives the compressed bytes the frame occupied (incl. a trailing index). */
+size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap);
+size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed);
+
+/* ---- one LZ4 frame, buffers in host memory (pinned buffers from b2lz4_pinned_alloc make the copies fast) */
+size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap);
+size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, size_t* consumed);
+void*  b2lz4_pinned_alloc(size_t n);
+void   b2lz4_pinned_free(void* p);
+
+/* ---- XXH32 of a device / host buffer, seed 0 (replaces XXH32, xxhash.c:392-416) */
+size_t b2lz4_xxh32_device(b2lz4_ctx* ctx, const void* d_src, size_t n, uint32_t* out);
+size_t b2lz4_xxh32_host(b2lz4_ctx* ctx, const void* src, size_t n, uint32_t* out);
+
+size_t b2lz4_last_stats(const b2lz4_ctx* ctx, b2lz4_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

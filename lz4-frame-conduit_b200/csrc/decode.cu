@@ -1,0 +1,417 @@
+// decode.cu — LZ4 frame decoding on sm_100a: frame scan, sequence decoder, result reduction.
+//
+// Replaces, on this path (citations relative to /root/reference/):
+//   LZ4F_decompress block walk            lz4/lib/lz4frame.c:1371-1840   -> frame_scan_kernel
+//   LZ4_decompress_generic (safe loop)    lz4/lib/lz4.c:1653-2068        -> decode_chains_kernel
+//   block / content checksum verification lz4frame.c:1604-1611,1734-1745 -> xxh32 kernels (xxh32.cu)
+// Written from the format documents (lz4_Block_format.md, lz4_Frame_format.md) and the behaviour of
+// the reference decoder (its acceptance rules, lz4.c:1882-2035, are mirrored here).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------------
+// frame scan: header parse, block walk (or index-frame load), piece/chain tables.  One CTA.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_le32_dev(const uint8_t* p) { return ld32u(p); }
+
+// Validates the B2IX index frame that may follow the LZ4 frame and returns its payload pointer.
+__device__ const uint8_t* find_index(const uint8_t* src, uint64_t n, uint64_t* payload_bytes) {
+    if (n < 16 + sizeof(IndexHead) + HEADER_MIN) return nullptr;
+    if (ld_le32_dev(src + n - 4) != IDX_MAGIC) return nullptr;
+    uint64_t pb = ld_le32_dev(src + n - 8);                // bytes before the 8-byte trailer
+    if (pb < sizeof(IndexHead) || pb + 16 + HEADER_MIN > n) return nullptr;
+    const uint8_t* skip = src + n - 16 - pb;              // skippable header: magic, size
+    if (ld_le32_dev(skip) != IDX_SKIP_MAGIC) return nullptr;
+    if (ld_le32_dev(skip + 4) != pb + 8) return nullptr;
+    const uint8_t* payload = skip + 8;
+    if (ld_le32_dev(payload) != IDX_MAGIC || ld_le32_dev(payload + 4) != 1u) return nullptr;
+    *payload_bytes = pb;
+    return payload;
+}
+
+__global__ void __launch_bounds__(256)
+frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap, uint32_t mode,
+                  FrameIndex* __restrict__ fi, BlockRef* __restrict__ blocks, uint32_t cap_blocks,
+                  Piece* __restrict__ pieces, uint32_t cap_pieces, Chain* __restrict__ chains)
+{
+    __shared__ FrameIndex s;
+    __shared__ const uint8_t* s_idx;
+    __shared__ uint32_t s_bad;
+    const uint32_t tid = threadIdx.x;
+
+    if (tid == 0) {
+        s = FrameIndex{};
+        s_idx = nullptr; s_bad = 0;
+        uint8_t hdr[HEADER_MAX];
+        uint32_t hn = n < (uint64_t)HEADER_MAX ? (uint32_t)n : (uint32_t)HEADER_MAX;
+        for (uint32_t i = 0; i < hn; ++i) hdr[i] = src[i];
+        s.err = header_parse(hdr, hn, s.desc);
+        if (s.err == OK) {
+            s.block_size = block_size_of(s.desc.block_size_id);
+            if (mode & SCAN_USE_INDEX) {
+                uint64_t pb = 0;
+                const uint8_t* ix = find_index(src, n, &pb);
+                if (ix) {
+                    IndexHead h;
+                    for (uint32_t i = 0; i < sizeof(IndexHead) / 4; ++i) ((uint32_t*)&h)[i] = ld_le32_dev(ix + 4 * i);
+                    uint64_t want = sizeof(IndexHead) + (uint64_t)h.n_blocks * sizeof(IndexBlock)
+                                  + (uint64_t)h.n_chains * sizeof(IndexChain);
+                    if (want == pb && h.block_size == s.block_size && s.desc.block_independent &&
+                        h.n_chains >= h.n_blocks) {
+                        s_idx = ix;
+                        s.n_blocks = h.n_blocks; s.n_pieces = h.n_chains; s.n_chains = h.n_chains;
+                        s.total_out = h.content_size;
+                        s.consumed_with_index = n;
+                        s.consumed = n - 16 - pb;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (s.err != OK) { if (tid == 0) *fi = s; return; }
+
+    const uint32_t bc = s.desc.block_checksum ? 4u : 0u;
+    const uint32_t cc = s.desc.content_checksum ? 4u : 0u;
+
+    if (s_idx) {
+        // ---- indexed layout: everything is a prefix sum over the index entries (parallel).
+        const uint8_t* ix = s_idx;
+        const uint32_t nb = s.n_blocks, nc = s.n_chains;
+        if (nb > cap_blocks || nc > cap_pieces) {
+            if (tid == 0) { s.err = E_allocation_failed; s.need_blocks = nb; s.need_pieces = nc; *fi = s; }
+            return;
+        }
+        const uint8_t* ib = ix + sizeof(IndexHead);
+        const uint8_t* ic = ib + (uint64_t)nb * sizeof(IndexBlock);
+        // serial-per-thread ranges + smem scan of the partial sums (blocks are few: <= U / 64 KB)
+        __shared__ uint64_t part_src[256], part_dst[256];
+        __shared__ uint32_t part_cnt[256];
+        uint32_t per = (nb + 255u) / 256u;
+        uint32_t b0 = tid * per, b1 = b0 + per < nb ? b0 + per : nb;
+        uint64_t a = 0, d = 0;
+        uint32_t cnt = 0;
+        for (uint32_t b = b0; b < b1; ++b) {
+            uint32_t w = ld_le32_dev(ib + (uint64_t)b * sizeof(IndexBlock));
+            a += 4ull + (w & 0x7FFFFFFFu) + bc;
+            d += ld_le32_dev(ib + (uint64_t)b * sizeof(IndexBlock) + 4);
+            cnt += ld_le32_dev(ib + (uint64_t)b * sizeof(IndexBlock) + 12);
+        }
+        part_src[tid] = a; part_dst[tid] = d; part_cnt[tid] = cnt;
+        __syncthreads();
+        if (tid == 0) {
+            uint64_t ra = s.desc.header_size, rd = 0;
+            uint32_t rc = 0;
+            for (int i = 0; i < 256; ++i) {
+                uint64_t ta = part_src[i], td = part_dst[i]; uint32_t tc = part_cnt[i];
+                part_src[i] = ra; part_dst[i] = rd; part_cnt[i] = rc; ra += ta; rd += td; rc += tc;
+            }
+            // frame must end exactly where the index says: EndMark + optional checksum, then the index frame
+            if (ra + 4 + cc != s.consumed || rd != s.total_out || rc != nc) s_bad = 1;
+            else if (ld_le32_dev(src + ra) != 0u) s_bad = 1;
+            else if (cc) s.stored_content_checksum = ld_le32_dev(src + ra + 4);
+        }
+        __syncthreads();
+        a = part_src[tid]; d = part_dst[tid]; cnt = part_cnt[tid];
+        for (uint32_t b = b0; b < b1 && !s_bad; ++b) {
+            const uint8_t* e = ib + (uint64_t)b * sizeof(IndexBlock);
+            uint32_t w = ld_le32_dev(e), us = ld_le32_dev(e + 4), fc = ld_le32_dev(e + 8), ncb = ld_le32_dev(e + 12);
+            uint32_t cs = w & 0x7FFFFFFFu;
+            // the index is only a hint: the real frame bytes decide
+            if (ld_le32_dev(src + a) != w || cs == 0 || cs > s.block_size || us > s.block_size || us == 0 ||
+                ncb == 0 || fc != cnt || (uint64_t)fc + ncb > nc || ((w >> 31) && (ncb != 1 || cs != us))) { s_bad = 1; break; }
+            BlockRef br; br.src_off = a + 4; br.csize = cs; br.stored = w >> 31; br.dst_off = d; br.usize = us; br.pad = 0;
+            blocks[b] = br;
+            for (uint32_t k = 0; k < ncb; ++k) {
+                const uint8_t* ce = ic + (uint64_t)(fc + k) * sizeof(IndexChain);
+                uint32_t tok = ld_le32_dev(ce), out = ld_le32_dev(ce + 4);
+                uint32_t tok_n = cs, out_n = us;
+                if (k + 1 < ncb) { tok_n = ld_le32_dev(ce + 8); out_n = ld_le32_dev(ce + 12); }
+                if ((k == 0 && (tok != 0 || out != 0)) || tok >= tok_n || out > out_n || tok_n > cs || out_n > us) { s_bad = 1; break; }
+                Piece pc; pc.src_off = a + 4 + tok; pc.src_len = tok_n - tok;
+                pc.flags = PIECE_EXACT | (br.stored ? PIECE_STORED : 0u) | (k + 1 == ncb ? PIECE_ENDS_BLOCK : 0u);
+                pc.dst_len = out_n - out; pc.block = b; pc.dst_rel = out; pc.pad = 0;
+                pieces[fc + k] = pc;
+                Chain ch; ch.dst_off = d + out; ch.first_piece = fc + k; ch.n_pieces = 1;
+                chains[fc + k] = ch;
+            }
+            a += 4ull + cs + bc; d += us; cnt += ncb;
+        }
+        __syncthreads();
+        if (!s_bad) {
+            if (tid == 0) {
+                s.indexed = 1; s.layout_known = 1;
+                if (s.total_out > dst_cap) s.err = E_dstMaxSize_tooSmall;
+                if (s.desc.has_content_size && s.desc.content_size != s.total_out) s.err = E_frameSize_wrong;
+                *fi = s;
+            }
+            return;
+        }
+        // fall through to the serial walk with the index ignored
+        __syncthreads();
+        if (tid == 0) { s.n_blocks = s.n_pieces = s.n_chains = 0; s.total_out = 0; s.consumed = s.consumed_with_index = 0; }
+        __syncthreads();
+    }
+
+    if (tid == 0) {
+        // ---- serial walk over the block header words (lz4frame.c:1470-1500)
+        uint64_t ip = s.desc.header_size;
+        uint32_t nb = 0;
+        Err err = OK;
+        for (;;) {
+            if (n - ip < 4) { err = E_noEndMark; break; }
+            uint32_t w = ld_le32_dev(src + ip); ip += 4;
+            uint32_t cs = w & 0x7FFFFFFFu;
+            if (cs == 0) break;                                      // EndMark
+            if (cs > s.block_size) { err = E_maxBlockSize_invalid; break; }
+            if (n - ip < (uint64_t)cs + bc) { err = E_noEndMark; break; }
+            if (nb < cap_blocks && nb < cap_pieces) {
+                BlockRef br; br.src_off = ip; br.csize = cs; br.stored = w >> 31;
+                br.dst_off = (uint64_t)nb * s.block_size; br.usize = 0; br.pad = 0;
+                blocks[nb] = br;
+                Piece pc; pc.src_off = ip; pc.src_len = cs;
+                pc.flags = PIECE_ENDS_BLOCK | (br.stored ? PIECE_STORED : 0u);
+                pc.dst_len = 0; pc.block = nb; pc.dst_rel = 0; pc.pad = 0;
+                pieces[nb] = pc;
+                if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) { Chain ch; ch.dst_off = br.dst_off; ch.first_piece = nb; ch.n_pieces = 1; chains[nb] = ch; }
+            }
+            ++nb;
+            ip += (uint64_t)cs + bc;
+        }
+        if (err == OK && cc) {
+            if (n - ip < 4) err = E_noEndMark;
+            else { s.stored_content_checksum = ld_le32_dev(src + ip); ip += 4; }
+        }
+        s.need_blocks = nb; s.need_pieces = nb;
+        if (err == OK && (nb > cap_blocks || nb > cap_pieces)) err = E_allocation_failed;
+        s.err = err;
+        s.n_blocks = nb; s.n_pieces = nb;
+        s.consumed = ip; s.consumed_with_index = ip;
+        s.total_out = (uint64_t)nb * s.block_size;                   // upper bound
+        if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) { s.n_chains = nb; s.layout_known = 0; }
+        else {
+            s.n_chains = nb ? 1u : 0u; s.layout_known = 0;
+            if (nb && err == OK) { Chain ch; ch.dst_off = 0; ch.first_piece = 0; ch.n_pieces = nb; chains[0] = ch; }
+        }
+        *fi = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// sequence decoder: one warp per chain, pieces in order.
+// All lanes keep identical parse state (uniform control flow); literal and match copies are spread
+// over the 32 lanes.  Acceptance rules mirror the reference decoder's safe loop (lz4.c:1844-2055).
+// ------------------------------------------------------------------------------------------------
+struct Cursor {            // what the warp knows about the piece it is decoding
+    const uint8_t* src;    // compressed buffer base
+    uint8_t* dst;          // output buffer base
+    uint64_t ip, iend;     // current / end of this piece's compressed bytes
+    uint64_t iend_blk;     // end of the owning block's compressed bytes (reference's `iend`)
+    uint64_t op, oend;     // current output position / output limit of the owning block (reference's `oend`)
+    uint64_t opiece_end;   // exact end of this piece's output (PIECE_EXACT) or == oend
+    uint64_t low;          // lowest output offset a match may read (window start)
+};
+
+// returns 0 or an Err; c.op is advanced
+__device__ __forceinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
+{
+    const uint32_t lane = lane_id();
+    const uint8_t* __restrict__ src = c.src;
+    uint8_t* dst = c.dst;
+    uint64_t ip = c.ip, op = c.op;
+    const uint64_t iend = c.iend_blk;
+    uint32_t err = 0;
+    if (c.iend == ip) return E_decompressionFailed;                         // empty input (lz4.c:1702)
+    for (;;) {
+        if (ip >= c.iend) { err = E_decompressionFailed; break; }
+        uint32_t token = src[ip++];
+        uint64_t ll = token >> 4;
+        if (ll == 15) {                                                     // lz4.c:1882-1889
+            if (ip + 15 >= iend) { err = E_decompressionFailed; break; }
+            uint32_t sbyte;
+            do { sbyte = src[ip++]; ll += sbyte; if (ip + 15 >= iend) break; } while (sbyte == 255);
+        }
+        // last-sequence test (lz4.c:1906): not enough input for an offset + next token, or the
+        // literals reach the last 12 bytes of the block's output window
+        bool last = (op + ll + 12 > c.oend) || (ip + ll + 8 > iend);
+        if (last) {
+            if (ip + ll != iend || op + ll > c.oend || !ends_block || op + ll > c.opiece_end || iend != c.iend) {
+                err = E_decompressionFailed; break;
+            }
+        } else if (ip + ll + 2 > c.iend || op + ll > c.opiece_end) { err = E_decompressionFailed; break; }
+        // literals
+        {
+            const uint8_t* s = src + ip; uint8_t* d = dst + op;
+            if (ll <= 32) { if (lane < ll) d[lane] = s[lane]; }
+            else group_copy(d, s, ll, lane, 32);
+        }
+        ip += ll; op += ll;
+        if (last) break;
+        uint32_t offset = (uint32_t)src[ip] | ((uint32_t)src[ip + 1] << 8);
+        ip += 2;
+        uint64_t ml = token & 15u;
+        if (ml == 15) {                                                     // lz4.c:1967-1972
+            uint32_t sbyte; bool bad = false;
+            do { sbyte = src[ip++]; ml += sbyte; if (ip + 4 >= iend) { bad = true; break; } } while (sbyte == 255);
+            if (bad) { err = E_decompressionFailed; break; }
+        }
+        ml += 4;
+        if (offset == 0 || (uint64_t)offset > op - c.low) { err = E_decompressionFailed; break; }   // lz4.c:1977
+        if (op + ml + 5 > c.oend || op + ml > c.opiece_end) { err = E_decompressionFailed; break; }   // lz4.c:2033-2035
+        // match copy: the source window [op-offset, op) is final (earlier sequences of this chain);
+        // overlapping matches replicate it with period `offset`.
+        __syncwarp();
+        {
+            uint8_t* d = dst + op;
+            const uint8_t* m = d - offset;
+            if (offset >= ml) {
+                if (ml <= 32) { if (lane < ml) d[lane] = m[lane]; }
+                else group_copy(d, m, ml, lane, 32);
+            } else if (offset >= 32 || ml <= 32) {
+                // period >= 32 or short: lane i copies i, i+32, ... from inside the final window
+                for (uint64_t i = lane; i < ml; i += 32) d[i] = m[i % offset];
+            } else {
+                // short period, long run (offset < 32 < ml): each lane owns byte positions i = lane + 32k;
+                // its source index inside the pattern advances by 32 mod offset every step.
+                uint32_t r = lane % offset, step = 32u % offset;
+                for (uint64_t i = lane; i < ml; i += 32) {
+                    d[i] = m[r];
+                    r += step; if (r >= offset) r -= offset;
+                }
+            }
+        }
+        __syncwarp();
+        op += ml;
+        if (ip == c.iend && !ends_block) {                                  // sub-block ends after a match
+            if (op != c.opiece_end) err = E_decompressionFailed;
+            break;
+        }
+    }
+    c.ip = ip; c.op = op;
+    return err;
+}
+
+__global__ void __launch_bounds__(DEC_WARPS * 32)
+decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint64_t dst_cap,
+                     const FrameIndex* __restrict__ fi, const BlockRef* __restrict__ blocks,
+                     const Piece* __restrict__ pieces, const Chain* __restrict__ chains,
+                     PieceOut* __restrict__ outs, uint32_t* __restrict__ ticket)
+{
+    if (fi->err != OK) return;
+    const uint32_t lane = lane_id();
+    const uint32_t n_chains = fi->n_chains;
+    const uint32_t block_size = fi->block_size;
+    const bool linked = !fi->desc.block_independent;
+    for (;;) {
+        uint32_t c = 0;
+        if (lane == 0) c = atomicAdd(ticket, 1u);
+        c = __shfl_sync(FULL_MASK, c, 0);
+        if (c >= n_chains) break;
+        const Chain ch = chains[c];
+        uint64_t op = ch.dst_off;
+        const uint64_t chain_start = ch.dst_off;
+        bool dead = false;
+        for (uint32_t k = 0; k < ch.n_pieces; ++k) {
+            const uint32_t pi = ch.first_piece + k;
+            const Piece pc = pieces[pi];
+            PieceOut po; po.out_len = 0; po.err = 0;
+            if (dead) { po.err = E_decompressionFailed; if (lane == 0) outs[pi] = po; continue; }
+            const BlockRef br = blocks[pc.block];
+            // output window of the owning block (the reference hands maxBlockSize as capacity, lz4frame.c:1670)
+            uint64_t blk_out = (pc.flags & PIECE_EXACT) ? br.dst_off : op;
+            uint64_t oend = blk_out + block_size;
+            if (blk_out >= dst_cap) oend = blk_out; else if (oend > dst_cap) oend = dst_cap;
+            if (pc.flags & PIECE_STORED) {
+                if (op + pc.src_len > dst_cap) po.err = E_dstMaxSize_tooSmall;
+                else {
+                    group_copy(dst + op, src + pc.src_off, pc.src_len, lane, 32);
+                    po.out_len = pc.src_len; op += pc.src_len;
+                }
+            } else {
+                Cursor cu;
+                cu.src = src; cu.dst = dst;
+                cu.ip = pc.src_off; cu.iend = pc.src_off + pc.src_len;
+                cu.iend_blk = br.src_off + br.csize;
+                cu.op = op; cu.oend = oend;
+                cu.opiece_end = (pc.flags & PIECE_EXACT) ? op + pc.dst_len : oend;
+                // window start: independent blocks/sub-blocks may only reference their own output;
+                // linked blocks reach up to 64 KB into the earlier output of the chain (lz4frame.c:1286-1349)
+                cu.low = linked ? chain_start : op;
+                uint32_t e = decode_piece(cu, (pc.flags & PIECE_ENDS_BLOCK) != 0);
+                if ((pc.flags & PIECE_EXACT) && e == 0 && cu.op - op != pc.dst_len) e = E_decompressionFailed;
+                if (e && oend - blk_out < block_size) e = E_dstMaxSize_tooSmall;   // ran out of destination
+                po.err = e; po.out_len = (uint32_t)(cu.op - op);
+                op = cu.op;
+            }
+            if (po.err) dead = true;
+            if (lane == 0) outs[pi] = po;
+            __syncwarp();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// result reduction: first error in block order, total size, layout check.  One CTA.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+decode_finalize_kernel(const FrameIndex* __restrict__ fi, const Piece* __restrict__ pieces,
+                       const PieceOut* __restrict__ outs, const uint32_t* __restrict__ block_crc_bad,
+                       DecodeResult* __restrict__ res, uint32_t* __restrict__ ticket)
+{
+    __shared__ uint32_t s_first_bad, s_short;
+    __shared__ unsigned long long s_total;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) { s_first_bad = 0xFFFFFFFFu; s_short = 0xFFFFFFFFu; s_total = 0; *ticket = 0; }
+    __syncthreads();
+    if (fi->err != OK) {
+        if (tid == 0) { DecodeResult r{}; r.err = fi->err; r.layout_ok = 1; *res = r; }
+        return;
+    }
+    const uint32_t np = fi->n_pieces, nb = fi->n_blocks, bs = fi->block_size;
+    unsigned long long tot = 0;
+    for (uint32_t i = tid; i < np; i += blockDim.x) {
+        PieceOut po = outs[i];
+        if (po.err) atomicMin(&s_first_bad, i);
+        tot += po.out_len;
+    }
+    // a non-final block that decodes short breaks the "block b starts at b*block_size" layout
+    if (!fi->layout_known && fi->n_chains == nb) {
+        for (uint32_t i = tid; i + 1 < nb; i += blockDim.x)
+            if (outs[i].err == 0 && outs[i].out_len != bs) atomicMin(&s_short, i);
+    }
+    atomicAdd(&s_total, tot);
+    __syncthreads();
+    if (tid == 0) {
+        DecodeResult r{};
+        r.layout_ok = (s_short == 0xFFFFFFFFu);
+        r.total_out = s_total;
+        uint32_t crc_bad = block_crc_bad ? *block_crc_bad : 0xFFFFFFFFu;
+        uint32_t bad_piece_block = s_first_bad == 0xFFFFFFFFu ? 0xFFFFFFFFu : pieces[s_first_bad].block;
+        if (crc_bad != 0xFFFFFFFFu && crc_bad <= bad_piece_block) { r.err = E_blockChecksum_invalid; r.err_block = crc_bad; }
+        else if (bad_piece_block != 0xFFFFFFFFu) { r.err = outs[s_first_bad].err; r.err_block = bad_piece_block; }
+        if (r.err == OK && fi->desc.has_content_size && r.layout_ok && fi->desc.content_size != r.total_out)
+            r.err = E_frameSize_wrong;                                      // lz4frame.c:1715-1716
+        *res = r;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// block checksum verification (lz4frame.c:1604-1611): XXH32 over each block's stored bytes.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+verify_block_checksums_kernel(const uint8_t* __restrict__ src, const FrameIndex* __restrict__ fi,
+                              const BlockRef* __restrict__ blocks, uint32_t* __restrict__ first_bad)
+{
+    if (fi->err != OK || !fi->desc.block_checksum) return;
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t stride = gridDim.x * blockDim.x;
+    for (; b < fi->n_blocks; b += stride) {
+        BlockRef br = blocks[b];
+        uint32_t h = xxh32_thread(src + br.src_off, br.csize);
+        if (h != ld32u(src + br.src_off + br.csize)) atomicMin(first_bad, b);
+    }
+}
+
+}  // namespace b2

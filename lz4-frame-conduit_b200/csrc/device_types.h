@@ -1,0 +1,143 @@
+// device_types.h — plain structs shared by the host engine and the sm_100a kernels.
+#pragma once
+#include <stdint.h>
+#include "format.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------ decode side
+// One LZ4 frame block as found by the frame scan (lz4frame.c:1475-1500 walks the same words).
+struct BlockRef {
+    uint64_t src_off;     // offset of the block's data bytes inside the compressed buffer
+    uint32_t csize;       // stored/compressed size in bytes (flag stripped)
+    uint32_t stored;      // 1 = raw (uncompressed) block
+    uint64_t dst_off;     // where the block's output starts (valid when the layout is known up front)
+    uint32_t usize;       // decoded size if known up front (index present), else 0
+    uint32_t pad;
+};
+
+// A piece = a run of whole LZ4 sequences decoded in order by one warp.
+//   foreign frame: piece = block;   indexed frame (ours): piece = independent sub-block of a block.
+enum : uint32_t { PIECE_STORED = 1u, PIECE_ENDS_BLOCK = 2u, PIECE_EXACT = 4u };
+struct Piece {
+    uint64_t src_off;     // first token of the piece (absolute offset in the compressed buffer)
+    uint32_t src_len;     // compressed bytes of the piece
+    uint32_t flags;
+    uint32_t dst_len;     // expected decoded bytes (PIECE_EXACT) — else unused
+    uint32_t block;       // owning block (for the block-level limits the reference's checks use)
+    uint32_t dst_rel;     // offset of the piece's output inside its block's output (PIECE_EXACT)
+    uint32_t pad;
+};
+
+// A chain = consecutive pieces decoded by ONE warp into contiguous output.
+//   independent blocks: one chain per piece;  linked-block frame: one chain for the whole frame.
+struct Chain {
+    uint64_t dst_off;     // first output byte of the chain
+    uint32_t first_piece;
+    uint32_t n_pieces;
+};
+
+struct PieceOut {
+    uint32_t out_len;     // decoded bytes
+    uint32_t err;         // 0 = ok, else b2::Err
+};
+
+// Result of the frame scan; lives in device memory and is mirrored to the host once per call.
+struct FrameIndex {
+    uint32_t err;             // b2::Err of the scan
+    uint32_t n_blocks;
+    uint32_t n_pieces;
+    uint32_t n_chains;
+    uint32_t block_size;      // bytes
+    uint32_t indexed;         // 1 = a valid B2IX index frame followed the frame and was used
+    uint32_t layout_known;    // 1 = every block's dst_off is final before decoding
+    uint32_t stored_content_checksum;
+    uint64_t consumed;        // compressed bytes from frame start through EndMark (+ content checksum)
+    uint64_t consumed_with_index;   // ... plus the trailing index frame when present
+    uint64_t total_out;       // decoded size when known up front (indexed), else upper bound n_blocks*block_size
+    uint32_t need_blocks;     // table sizes the scan wanted (for the retry after E_allocation_failed)
+    uint32_t need_pieces;
+    FrameDesc desc;
+};
+
+// Decode summary written by the finalise kernel
+struct DecodeResult {
+    uint32_t err;             // first error in block order (b2::Err), 0 = ok
+    uint32_t err_block;
+    uint64_t total_out;
+    uint32_t content_checksum;    // XXH32 of the output when the frame carries one (computed on device)
+    uint32_t layout_ok;           // 0 = a non-final block decoded short while the layout assumed full blocks
+};
+
+// ------------------------------------------------------------------ encode side
+struct EncParams {
+    uint64_t n;               // uncompressed bytes in this call
+    uint32_t block_size;
+    uint32_t sub_size;        // independent sub-block size (divides block_size)
+    uint32_t subs_per_block;
+    uint32_t n_blocks;
+    uint32_t n_subs;          // total sub-blocks
+    uint32_t scratch_stride;  // bytes of scratch per sub-block
+    uint32_t block_checksum;
+    uint32_t content_checksum;
+    uint32_t write_header;    // 1 = emit frame header (+ EndMark, checksum slot, index) around the blocks
+    uint32_t write_index;     // 1 = append the B2IX skippable index frame
+    FrameDesc desc;
+};
+
+struct SubOut {               // written by the match finder, one per sub-block
+    uint32_t out_len;         // bytes emitted into scratch
+    uint32_t first_ll;        // literal length of the first emitted sequence
+    uint32_t first_hdr;       // token + length bytes of that first sequence
+    uint32_t tail;            // trailing literals NOT emitted (carried into the next sub-block)
+    uint32_t emitted;         // 0 = no sequence at all (whole sub-block is carried literals)
+    uint32_t n_seq;
+};
+
+struct SubPlace {             // written by the layout kernel
+    uint32_t dst_rel;         // offset of this sub-block's bytes inside the block's compressed data
+    uint32_t carry_in;        // literals inherited from the previous sub-block(s)
+    uint32_t new_hdr;         // size of the re-encoded first token + length bytes
+    uint32_t size;            // final bytes of this sub-block inside the block
+};
+
+struct BlockPlace {
+    uint64_t frame_off;       // offset of the block's 4-byte header word inside the output
+    uint32_t csize;           // bytes of block data (== usize when stored)
+    uint32_t stored;
+    uint32_t usize;
+    uint32_t n_chain;         // emitted sub-blocks (index entries)
+    uint32_t first_chain;
+    uint32_t pad;
+};
+
+struct EncodeResult {
+    uint32_t err;
+    uint32_t n_blocks;
+    uint64_t frame_len;           // total bytes written (incl. index frame when requested)
+    uint64_t blocks_len;          // bytes of the block region only
+    uint64_t content_checksum_off;// where the u32 content checksum goes (0 = none)
+    uint64_t index_off;           // where the index frame starts (0 = none)
+    uint32_t n_chains;
+    uint32_t pad;
+};
+
+// XXH32 streaming state kept in device memory for the pipelined content checksum (xxhash.c:437-554)
+struct XxhState {
+    uint32_t v[4];
+    uint32_t mem[4];
+    uint32_t memsize;
+    uint32_t total_len;   // wraps mod 2^32 like the reference (xxhash.c:464)
+    uint32_t large;
+    uint32_t pad;
+};
+
+// ---- B2IX index frame (a skippable frame, lz4_Frame_format.md:298-335, appended after the LZ4 frame).
+// payload: IndexHead | n_blocks * IndexBlock | n_chains * IndexChain | u32 payload_bytes | u32 IDX_MAGIC
+constexpr uint32_t IDX_SKIP_MAGIC = 0x184D2A5Bu;
+constexpr uint32_t IDX_MAGIC      = 0x58493242u;   // "B2IX"
+struct IndexHead  { uint32_t magic, version, block_size, n_blocks, n_chains, reserved; uint64_t content_size; };
+struct IndexBlock { uint32_t hdr_word, usize, first_chain, n_chain; };
+struct IndexChain { uint32_t tok_off, out_off; };   // relative to the block's data / the block's output
+
+}  // namespace b2

@@ -1,0 +1,348 @@
+// encode.cu — LZ4 frame encoding on sm_100a: warp-cooperative hash match finder + sequence emitter,
+// block layout (prefix sums, stored-block decision, frame header / EndMark / index) and gather.
+//
+// Replaces, on this path (citations relative to /root/reference/):
+//   LZ4_compress_generic (greedy hash match finder + token emitter)   lz4/lib/lz4.c:789-1177
+//   LZ4F_makeBlock (block header word, stored-block fallback)         lz4/lib/lz4frame.c:739-761
+//   LZ4F_compressBegin / LZ4F_compressEnd (header, EndMark)           lz4frame.c:600-702, 984-1018
+// This is NOT a port of that code: the reference walks one position at a time with a 4 K-entry table;
+// here one warp probes 32 positions per step against an 8 K-entry shared-memory table, a 4 MB frame
+// block is cut into independent sub-blocks (one warp each) whose outputs are stitched by prefix sums,
+// and the only things kept from the reference are the *format rules* every LZ4 encoder must obey
+// (lz4_Block_format.md:108-129: last 5 bytes literal, last match starts >= 12 bytes before the end,
+// inputs < 13 bytes are literal-only, offsets <= 65535) and the stored-block rule of the frame layer
+// (a block is stored raw iff it does not compress to fewer bytes, lz4frame.c:746-752).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b2 {
+
+constexpr uint32_t HSIZE = 1u << ENC_HLOG;
+
+size_t find_emit_smem_bytes() { return (size_t)ENC_WARPS * HSIZE * sizeof(uint16_t); }
+
+__device__ __forceinline__ uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - ENC_HLOG); }
+
+__device__ __forceinline__ uint32_t len_bytes(uint32_t v) {      // extra length bytes for a field value v
+    return v >= 15u ? (v - 15u) / 255u + 1u : 0u;
+}
+
+// token nibble already written by the caller; writes the 255-run + remainder bytes, returns new offset
+__device__ __forceinline__ uint32_t put_len_ext(uint8_t* out, uint32_t o, uint32_t v, uint32_t lane) {
+    if (v < 15u) return o;
+    uint32_t r = v - 15u, n255 = r / 255u;
+    for (uint32_t i = lane; i < n255; i += 32) out[o + i] = 255;
+    if (lane == 0) out[o + n255] = (uint8_t)(r - n255 * 255u);
+    return o + n255 + 1u;
+}
+
+// One sequence: token, literal length bytes, literals, offset, match length bytes (lz4_Block_format.md:27-105)
+__device__ __forceinline__ uint32_t emit_sequence(uint8_t* out, uint32_t o, const uint8_t* lit, uint32_t ll,
+                                                  uint32_t off, uint32_t mlc, uint32_t lane) {
+    if (lane == 0) out[o] = (uint8_t)(((ll < 15u ? ll : 15u) << 4) | (mlc < 15u ? mlc : 15u));
+    o = put_len_ext(out, o + 1, ll, lane);
+    if (ll <= 32) { if (lane < ll) out[o + lane] = lit[lane]; }
+    else group_copy(out + o, lit, ll, lane, 32);
+    o += ll;
+    if (lane == 0) { out[o] = (uint8_t)off; out[o + 1] = (uint8_t)(off >> 8); }
+    return put_len_ext(out, o + 2, mlc, lane);
+}
+
+// ------------------------------------------------------------------------------------------------
+// match finder + emitter: one warp per independent sub-block.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(ENC_WARPS * 32)
+find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restrict__ scratch,
+                 SubOut* __restrict__ subs, uint32_t* __restrict__ ticket)
+{
+    extern __shared__ __align__(16) uint16_t s_tab[];
+    const uint32_t lane = lane_id();
+    uint16_t* tab = s_tab + (threadIdx.x >> 5) * HSIZE;
+
+    for (;;) {
+        uint32_t s = 0;
+        if (lane == 0) s = atomicAdd(ticket, 1u);
+        s = __shfl_sync(FULL_MASK, s, 0);
+        if (s >= P.n_subs) break;
+
+        const uint32_t blk = s / P.subs_per_block, j = s - blk * P.subs_per_block;
+        const uint64_t blk_start = (uint64_t)blk * P.block_size;
+        const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
+        const uint32_t b0 = j * P.sub_size;
+        const uint32_t b1 = (b0 + P.sub_size < usize) ? b0 + P.sub_size : usize;
+        const bool last_sub = (b1 == usize);
+        const uint8_t* __restrict__ base = src + blk_start;
+        uint8_t* out = scratch + (uint64_t)s * P.scratch_stride;
+
+        // zero the table so the parse is deterministic
+        { uint4 z = make_uint4(0, 0, 0, 0); uint4* t4 = (uint4*)tab;
+          for (uint32_t i = lane; i < HSIZE * 2 / 16; i += 32) t4[i] = z; }
+        __syncwarp();
+
+        // positions that may start a match: p + 4 <= b1 and p <= usize - 12 (block end rule)
+        uint32_t limit = 0;
+        if (usize >= 13u) {
+            uint32_t la = b1 >= 3u ? b1 - 3u : 0u, lb = usize - 11u;
+            limit = la < lb ? la : lb;
+        }
+        const uint32_t matchlimit = (usize >= 5u) ? ((b1 < usize - 5u) ? b1 : usize - 5u) : 0u;
+
+        uint32_t ip = b0, anchor = b0, o = 0;
+        uint32_t miss = 0, nseq = 0, first_ll = 0, first_hdr = 0;
+
+        while (ip < limit) {
+            const uint32_t sl = (miss >> 2) < 3u ? (miss >> 2) : 3u;          // probe stride 1,2,4,8 after misses
+            const uint32_t p = ip + (lane << sl);
+            const bool valid = p < limit;
+            uint32_t v = 0, h = 0, rel = p - b0;
+            int32_t c = -1;
+            bool hit = false;
+            if (valid) {
+                v = ld32u(base + p);
+                h = hash4(v);
+                uint32_t cl = tab[h];
+                c = (int32_t)((rel & ~0xFFFFu) | cl);
+                if ((uint32_t)c >= rel) c -= 65536;
+                if (c >= 0 && rel - (uint32_t)c < 65536u) hit = (ld32u(base + b0 + c) == v);
+            }
+            __syncwarp();
+            if (valid) tab[h] = (uint16_t)rel;
+            __syncwarp();
+            const uint32_t m = __ballot_sync(FULL_MASK, hit);
+            if (m == 0) { ip += 32u << sl; ++miss; continue; }
+            miss = 0;
+            const int f = __ffs(m) - 1;
+            uint32_t mpos = __shfl_sync(FULL_MASK, p, f);
+            uint32_t cpos = b0 + (uint32_t)__shfl_sync(FULL_MASK, c, f);
+            // backward extension (up to 32 bytes), bounded by the pending literals and the sub-block start
+            {
+                uint32_t mb = mpos - anchor, cb = cpos - b0;
+                uint32_t maxback = mb < cb ? mb : cb;
+                bool eq = lane < maxback && base[mpos - 1 - lane] == base[cpos - 1 - lane];
+                uint32_t ne = __ballot_sync(FULL_MASK, !eq);
+                uint32_t back = ne ? (uint32_t)(__ffs(ne) - 1) : 32u;
+                mpos -= back; cpos -= back;
+            }
+            // forward extension: every lane compares 4 bytes; bytes at and after matchlimit never count
+            uint32_t len = 0;
+            for (;;) {
+                const uint32_t q = mpos + len + lane * 4u;
+                uint32_t avail = matchlimit > q ? matchlimit - q : 0u;
+                uint32_t nbytes = 0;
+                if (avail) {
+                    uint32_t x = ld32u(base + q) ^ ld32u(base + cpos + len + lane * 4u);
+                    nbytes = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4u;
+                    if (nbytes > avail) nbytes = avail;
+                }
+                const uint32_t part = __ballot_sync(FULL_MASK, nbytes != 4u);
+                if (part == 0) { len += 128u; continue; }
+                const int g = __ffs(part) - 1;
+                len += (uint32_t)g * 4u + __shfl_sync(FULL_MASK, nbytes, g);
+                break;
+            }
+            if (len < 4u) {                       // cannot happen for a verified candidate inside the limits;
+                ip = mpos + 1; continue;          // kept as a guard against emitting an invalid match
+            }
+            const uint32_t ll = mpos - anchor;
+            if (nseq == 0) { first_ll = ll; first_hdr = 1u + len_bytes(ll); }
+            o = emit_sequence(out, o, base + anchor, ll, mpos - cpos, len - 4u, lane);
+            ++nseq;
+            ip = mpos + len; anchor = ip;
+            // seed the table with a position near the end of the match (the reference does the same with ip-2)
+            if (lane == 0 && ip - 2u >= b0 + 0u && ip - 2u < limit) {
+                uint32_t pp = ip - 2u;
+                tab[hash4(ld32u(base + pp))] = (uint16_t)(pp - b0);
+            }
+            __syncwarp();
+        }
+
+        uint32_t tail = b1 - anchor;
+        if (last_sub) {                            // final literal-only sequence of the block
+            if (nseq == 0) { first_ll = tail; first_hdr = 1u + len_bytes(tail); }
+            if (lane == 0) out[o] = (uint8_t)((tail < 15u ? tail : 15u) << 4);
+            o = put_len_ext(out, o + 1, tail, lane);
+            if (tail <= 32) { if (lane < tail) out[o + lane] = base[anchor + lane]; }
+            else group_copy(out + o, base + anchor, tail, lane, 32);
+            o += tail; tail = 0; ++nseq;
+        }
+        if (lane == 0) {
+            SubOut so; so.out_len = o; so.first_ll = first_ll; so.first_hdr = first_hdr; so.tail = tail;
+            so.emitted = nseq ? 1u : 0u; so.n_seq = nseq;
+            subs[s] = so;
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// layout: per-block stitch sizes, stored decision, frame offsets (scan), header / EndMark / index.
+// One CTA of 1024 threads.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict__ places,
+              BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst, uint64_t dst_cap,
+              EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket)
+{
+    __shared__ uint64_t part_bytes[1024];
+    __shared__ uint32_t part_chain[1024];
+    __shared__ EncodeResult s_res;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t nb = P.n_blocks;
+    const uint32_t bc = P.block_checksum ? 4u : 0u;
+    const uint32_t per = (nb + 1023u) / 1024u;
+    const uint32_t b0 = tid * per < nb ? tid * per : nb, b1 = (b0 + per < nb) ? b0 + per : nb;
+    if (tid == 0) *ticket = 0;
+
+    uint64_t bytes = 0; uint32_t nchain = 0;
+    for (uint32_t b = b0; b < b1; ++b) {
+        const uint64_t blk_start = (uint64_t)b * P.block_size;
+        const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
+        const uint32_t ns = (usize + P.sub_size - 1u) / P.sub_size;
+        uint32_t carry = 0, off = 0, nc = 0;
+        for (uint32_t j = 0; j < ns; ++j) {
+            const uint32_t s = b * P.subs_per_block + j;
+            const SubOut so = subs[s];
+            SubPlace sp; sp.dst_rel = off; sp.carry_in = carry; sp.new_hdr = 0; sp.size = 0;
+            if (so.emitted) {
+                uint32_t ll2 = so.first_ll + carry;
+                sp.new_hdr = 1u + len_bytes(ll2);
+                sp.size = so.out_len - so.first_hdr + sp.new_hdr + carry;
+                off += sp.size; carry = so.tail; ++nc;
+            } else carry += so.tail;
+            places[s] = sp;
+        }
+        BlockPlace bp; bp.frame_off = 0; bp.usize = usize; bp.first_chain = 0; bp.pad = 0;
+        bp.stored = (off >= usize) ? 1u : 0u;                        // lz4frame.c:746-752
+        bp.csize = bp.stored ? usize : off;
+        bp.n_chain = bp.stored ? 1u : nc;
+        bplaces[b] = bp;
+        bytes += 4ull + bp.csize + bc; nchain += bp.n_chain;
+    }
+    part_bytes[tid] = bytes; part_chain[tid] = nchain;
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t hs = P.write_header ? (7u + (P.desc.has_content_size ? 8u : 0u) + (P.desc.has_dict_id ? 4u : 0u)) : 0u;
+        uint64_t run = hs; uint32_t rc = 0;
+        for (int i = 0; i < 1024; ++i) {
+            uint64_t t = part_bytes[i]; uint32_t c = part_chain[i];
+            part_bytes[i] = run; part_chain[i] = rc; run += t; rc += c;
+        }
+        EncodeResult r{};
+        r.n_blocks = nb; r.n_chains = rc;
+        r.blocks_len = run - hs;
+        uint64_t end = run;
+        if (P.write_header) {
+            end += 4;                                                // EndMark
+            if (P.content_checksum) { r.content_checksum_off = end; end += 4; }
+            if (P.write_index) {
+                r.index_off = end;
+                end += 8 + sizeof(IndexHead) + (uint64_t)nb * sizeof(IndexBlock) + (uint64_t)rc * sizeof(IndexChain) + 8;
+            }
+        }
+        r.frame_len = end;
+        r.err = end > dst_cap ? (uint32_t)E_dstMaxSize_tooSmall : (uint32_t)OK;
+        s_res = r; *res = r;
+        if (r.err == OK && P.write_header) {
+            uint8_t hdr[HEADER_MAX];
+            uint32_t n = header_write(hdr, P.desc);
+            for (uint32_t i = 0; i < n; ++i) dst[i] = hdr[i];
+            st_le32(dst + run, 0u);                                  // EndMark (lz4frame.c:998-1000)
+            if (r.index_off) {
+                uint8_t* x = dst + r.index_off;
+                uint32_t pb = (uint32_t)(sizeof(IndexHead) + (uint64_t)nb * sizeof(IndexBlock) + (uint64_t)rc * sizeof(IndexChain));
+                st_le32(x, IDX_SKIP_MAGIC); st_le32(x + 4, pb + 8u);
+                x += 8;
+                st_le32(x, IDX_MAGIC); st_le32(x + 4, 1u); st_le32(x + 8, P.block_size); st_le32(x + 12, nb);
+                st_le32(x + 16, rc); st_le32(x + 20, 0u);
+                st_le32(x + 24, (uint32_t)P.n); st_le32(x + 28, (uint32_t)(P.n >> 32));
+                st_le32(x + pb, pb); st_le32(x + pb + 4, IDX_MAGIC);
+            }
+        }
+    }
+    __syncthreads();
+    if (s_res.err != OK) return;
+    uint64_t run = part_bytes[tid]; uint32_t rc = part_chain[tid];
+    uint8_t* ib = s_res.index_off ? dst + s_res.index_off + 8 + sizeof(IndexHead) : nullptr;
+    uint8_t* ic = ib ? ib + (uint64_t)nb * sizeof(IndexBlock) : nullptr;
+    for (uint32_t b = b0; b < b1; ++b) {
+        BlockPlace bp = bplaces[b];
+        bp.frame_off = run; bp.first_chain = rc;
+        bplaces[b] = bp;
+        if (ib) {
+            uint8_t* e = ib + (uint64_t)b * sizeof(IndexBlock);
+            st_le32(e, bp.csize | (bp.stored << 31)); st_le32(e + 4, bp.usize);
+            st_le32(e + 8, rc); st_le32(e + 12, bp.n_chain);
+            uint8_t* ce = ic + (uint64_t)rc * sizeof(IndexChain);
+            if (bp.stored) { st_le32(ce, 0u); st_le32(ce + 4, 0u); }
+            else {
+                const uint32_t ns = (bp.usize + P.sub_size - 1u) / P.sub_size;
+                for (uint32_t j = 0; j < ns; ++j) {
+                    const uint32_t s = b * P.subs_per_block + j;
+                    if (!subs[s].emitted) continue;
+                    const SubPlace sp = places[s];
+                    st_le32(ce, sp.dst_rel); st_le32(ce + 4, j * P.sub_size - sp.carry_in);
+                    ce += sizeof(IndexChain);
+                }
+            }
+        }
+        run += 4ull + bp.csize + bc; rc += bp.n_chain;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// gather: one CTA per sub-block copies its bytes to their final place in the frame.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_kernel(const uint8_t* __restrict__ src, EncParams P, const uint8_t* __restrict__ scratch,
+              const SubOut* __restrict__ subs, const SubPlace* __restrict__ places,
+              const BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst,
+              const EncodeResult* __restrict__ res)
+{
+    if (res->err != OK) return;
+    const uint32_t tid = threadIdx.x, nt = blockDim.x;
+    for (uint32_t s = blockIdx.x; s < P.n_subs; s += gridDim.x) {
+        const uint32_t blk = s / P.subs_per_block, j = s - blk * P.subs_per_block;
+        const BlockPlace bp = bplaces[blk];
+        const uint64_t blk_start = (uint64_t)blk * P.block_size;
+        const uint32_t b0 = j * P.sub_size;
+        const uint32_t b1 = (b0 + P.sub_size < bp.usize) ? b0 + P.sub_size : bp.usize;
+        uint8_t* data = dst + bp.frame_off + 4;
+        if (j == 0 && tid == 0) st_le32(dst + bp.frame_off, bp.csize | (bp.stored << 31));
+        if (bp.stored) {
+            group_copy(data + b0, src + blk_start + b0, b1 - b0, tid, nt);
+            continue;
+        }
+        const SubOut so = subs[s];
+        if (!so.emitted) continue;
+        const SubPlace sp = places[s];
+        const uint8_t* sc = scratch + (uint64_t)s * P.scratch_stride;
+        uint8_t* out = data + sp.dst_rel;
+        if (sp.carry_in == 0) { group_copy(out, sc, so.out_len, tid, nt); continue; }
+        // re-encode the first token with the literals carried in from the previous sub-block(s)
+        const uint32_t ll2 = so.first_ll + sp.carry_in;
+        if (tid == 0) out[0] = (uint8_t)(((ll2 < 15u ? ll2 : 15u) << 4) | (sc[0] & 15u));
+        if (ll2 >= 15u) {
+            uint32_t r = ll2 - 15u, n255 = r / 255u;
+            for (uint32_t i = tid; i < n255; i += nt) out[1 + i] = 255;
+            if (tid == 0) out[1 + n255] = (uint8_t)(r - n255 * 255u);
+        }
+        group_copy(out + sp.new_hdr, src + blk_start + b0 - sp.carry_in, sp.carry_in, tid, nt);
+        group_copy(out + sp.new_hdr + sp.carry_in, sc + so.first_hdr, so.out_len - so.first_hdr, tid, nt);
+    }
+}
+
+// block checksums (lz4frame.c:756-759): XXH32 over the block's stored bytes, appended after them
+__global__ void __launch_bounds__(128)
+block_checksums_kernel(EncParams P, const BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst,
+                       const EncodeResult* __restrict__ res)
+{
+    if (res->err != OK || !P.block_checksum) return;
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    for (; b < P.n_blocks; b += gridDim.x * blockDim.x) {
+        const BlockPlace bp = bplaces[b];
+        uint32_t h = xxh32_thread(dst + bp.frame_off + 4, bp.csize);
+        st_le32(dst + bp.frame_off + 4 + bp.csize, h);
+    }
+}
+
+}  // namespace b2

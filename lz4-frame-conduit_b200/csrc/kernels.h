@@ -1,0 +1,46 @@
+// kernels.h — launch-side declarations of the sm_100a kernels (decode.cu, encode.cu, xxh32.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "device_types.h"
+
+namespace b2 {
+
+constexpr int DEC_WARPS = 4;          // warps per CTA in the sequence decoder
+constexpr int ENC_WARPS = 4;          // warps per CTA in the match finder (one hash table each)
+constexpr int ENC_HLOG  = 13;         // 8192-entry u16 hash table per warp (16 KB)
+enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u };
+
+// ---- decode
+__global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_cap, uint32_t mode,
+                                  FrameIndex* fi, BlockRef* blocks, uint32_t cap_blocks,
+                                  Piece* pieces, uint32_t cap_pieces, Chain* chains);
+__global__ void decode_chains_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap,
+                                     const FrameIndex* fi, const BlockRef* blocks, const Piece* pieces,
+                                     const Chain* chains, PieceOut* outs, uint32_t* ticket);
+__global__ void decode_finalize_kernel(const FrameIndex* fi, const Piece* pieces, const PieceOut* outs,
+                                       const uint32_t* block_crc_bad, DecodeResult* res, uint32_t* ticket);
+__global__ void verify_block_checksums_kernel(const uint8_t* src, const FrameIndex* fi,
+                                              const BlockRef* blocks, uint32_t* first_bad);
+
+// ---- encode
+__global__ void find_emit_kernel(const uint8_t* src, EncParams P, uint8_t* scratch, SubOut* subs, uint32_t* ticket);
+__global__ void layout_kernel(EncParams P, const SubOut* subs, SubPlace* places, BlockPlace* bplaces,
+                              uint8_t* dst, uint64_t dst_cap, EncodeResult* res, uint32_t* ticket);
+__global__ void gather_kernel(const uint8_t* src, EncParams P, const uint8_t* scratch, const SubOut* subs,
+                              const SubPlace* places, const BlockPlace* bplaces, uint8_t* dst,
+                              const EncodeResult* res);
+__global__ void block_checksums_kernel(EncParams P, const BlockPlace* bplaces, uint8_t* dst, const EncodeResult* res);
+
+// ---- XXH32
+__global__ void xxh32_stream_kernel(const uint8_t* data, uint64_t n, const uint64_t* n_ptr,
+                                    const uint32_t* enable_ptr, XxhState* st);                // update (1 CTA x 256)
+__global__ void xxh32_digest_kernel(const XxhState* st, uint32_t* out, uint8_t* base, const uint64_t* off_ptr);
+__global__ void content_check_kernel(const FrameIndex* fi, const XxhState* st, DecodeResult* res);
+__global__ void xxh32_reset_kernel(XxhState* st);
+__global__ void xxh32_many_kernel(const uint8_t* data, const uint64_t* offs, const uint32_t* lens,
+                                  uint32_t n, uint32_t* out);                                 // one hash per range
+
+size_t find_emit_smem_bytes();
+
+}  // namespace b2

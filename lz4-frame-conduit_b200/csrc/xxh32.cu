@@ -1,0 +1,132 @@
+// xxh32.cu — XXH32 on sm_100a (seed 0 everywhere on this path).
+//
+// Replaces XXH32 / XXH32_reset / XXH32_update / XXH32_digest (lz4/lib/xxhash.c:392-416, 437-554) where
+// the frame layer uses them: per-block checksums (many independent hashes, one thread each — see
+// xxh32_thread in common.cuh) and the per-frame content checksum.  The content checksum is a single
+// serial recurrence (4 accumulators, xxhash.c:269-275): it cannot be split across threads, so the
+// stream kernel below uses ONE hashing thread fed from shared memory while the rest of the CTA
+// prefetches the next tile; it is meant to run on its own stream, overlapped with the codec kernels.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b2 {
+
+constexpr uint32_t XXH_TILE = 16384;      // bytes per staged tile (two tiles in shared memory)
+
+__global__ void xxh32_reset_kernel(XxhState* st) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        XxhState s{};
+        s.v[0] = XP1 + XP2; s.v[1] = XP2; s.v[2] = 0; s.v[3] = 0u - XP1;     // xxhash.c:437-449
+        *st = s;
+    }
+}
+
+// XXH32_update over data[0, n) (xxhash.c:452-526).  Launch with ONE CTA of 256 threads.
+__global__ void __launch_bounds__(256)
+xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t* __restrict__ n_ptr,
+                    const uint32_t* __restrict__ enable_ptr, XxhState* __restrict__ st)
+{
+    if (enable_ptr && !*enable_ptr) return;      // e.g. &FrameIndex::desc.content_checksum
+    if (n_ptr) n = *n_ptr;                        // e.g. &DecodeResult::total_out
+    __shared__ __align__(16) uint8_t tile[2][XXH_TILE];
+    __shared__ XxhState s;
+    __shared__ uint64_t s_pos;          // first byte of the full-stripe region
+    __shared__ uint64_t s_stripes;      // number of 16-byte stripes in it
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) {
+        s = *st;
+        s.total_len += (uint32_t)n;                                           // wraps mod 2^32 by design
+        s.large |= (uint32_t)((n >= 16) | (s.total_len >= 16));
+        uint64_t pos = 0;
+        if (s.memsize + n < 16) {                                             // not a full stripe yet
+            for (uint64_t i = 0; i < n; ++i) ((uint8_t*)s.mem)[s.memsize + i] = data[i];
+            s.memsize += (uint32_t)n;
+            pos = n;
+        } else if (s.memsize) {                                               // complete the pending stripe
+            uint32_t take = 16 - s.memsize;
+            for (uint32_t i = 0; i < take; ++i) ((uint8_t*)s.mem)[s.memsize + i] = data[i];
+            for (int k = 0; k < 4; ++k) s.v[k] = xxh32_round(s.v[k], s.mem[k]);
+            s.memsize = 0;
+            pos = take;
+        }
+        s_pos = pos;
+        s_stripes = (n - pos) >> 4;
+    }
+    __syncthreads();
+    const uint64_t pos = s_pos, stripes = s_stripes;
+    const uint64_t ntiles = (stripes * 16 + XXH_TILE - 1) / XXH_TILE;
+    uint32_t v1 = s.v[0], v2 = s.v[1], v3 = s.v[2], v4 = s.v[3];
+    if (ntiles) {
+        uint64_t len0 = stripes * 16 < XXH_TILE ? stripes * 16 : XXH_TILE;
+        group_copy(tile[0], data + pos, len0, tid, 256);
+    }
+    __syncthreads();
+    for (uint64_t t = 0; t < ntiles; ++t) {
+        const uint64_t off = t * XXH_TILE;
+        const uint64_t len = (stripes * 16 - off) < XXH_TILE ? (stripes * 16 - off) : XXH_TILE;
+        if (t + 1 < ntiles) {                                                 // prefetch the next tile
+            const uint64_t off2 = off + XXH_TILE;
+            const uint64_t len2 = (stripes * 16 - off2) < XXH_TILE ? (stripes * 16 - off2) : XXH_TILE;
+            if (tid >= 32) group_copy(tile[(t + 1) & 1], data + pos + off2, len2, tid - 32, 224);
+        }
+        if (tid == 0) {
+            const uint4* w = (const uint4*)tile[t & 1];
+            const uint32_t ns = (uint32_t)(len >> 4);
+            #pragma unroll 4
+            for (uint32_t i = 0; i < ns; ++i) {
+                uint4 x = w[i];
+                v1 = xxh32_round(v1, x.x); v2 = xxh32_round(v2, x.y);
+                v3 = xxh32_round(v3, x.z); v4 = xxh32_round(v4, x.w);
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        s.v[0] = v1; s.v[1] = v2; s.v[2] = v3; s.v[3] = v4;
+        uint64_t done = pos + stripes * 16;
+        if (done < n) {                                                       // keep the remainder for later
+            uint32_t rem = (uint32_t)(n - done);
+            for (uint32_t i = 0; i < rem; ++i) ((uint8_t*)s.mem)[i] = data[done + i];
+            s.memsize = rem;
+        }
+        *st = s;
+    }
+}
+
+// XXH32_digest (xxhash.c:529-554); optionally stores the value little-endian at base + *off_ptr
+__global__ void xxh32_digest_kernel(const XxhState* __restrict__ st, uint32_t* __restrict__ out,
+                                    uint8_t* base, const uint64_t* off_ptr)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    XxhState s = *st;
+    uint32_t h = s.large ? xxh32_merge(s.v[0], s.v[1], s.v[2], s.v[3]) : s.v[2] + XP5;
+    h += s.total_len;
+    h = xxh32_tail(h, (const uint8_t*)s.mem, s.memsize);
+    if (out) *out = h;
+    if (base && off_ptr && *off_ptr) st_le32(base + *off_ptr, h);
+}
+
+// decode side: compare the digest with the checksum stored in the frame (lz4frame.c:1734-1745)
+__global__ void content_check_kernel(const FrameIndex* __restrict__ fi, const XxhState* __restrict__ st,
+                                     DecodeResult* __restrict__ res)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    if (fi->err != OK || !fi->desc.content_checksum) return;
+    XxhState s = *st;
+    uint32_t h = s.large ? xxh32_merge(s.v[0], s.v[1], s.v[2], s.v[3]) : s.v[2] + XP5;
+    h += s.total_len;
+    h = xxh32_tail(h, (const uint8_t*)s.mem, s.memsize);
+    res->content_checksum = h;
+    if (res->err == OK && res->layout_ok && h != fi->stored_content_checksum) res->err = E_contentChecksum_invalid;
+}
+
+// one hash per (offset, length) range, one thread each
+__global__ void __launch_bounds__(128)
+xxh32_many_kernel(const uint8_t* __restrict__ data, const uint64_t* __restrict__ offs,
+                  const uint32_t* __restrict__ lens, uint32_t n, uint32_t* __restrict__ out)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i < n; i += gridDim.x * blockDim.x) out[i] = xxh32_thread(data + offs[i], lens[i]);
+}
+
+}  // namespace b2

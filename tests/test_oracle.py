@@ -1,0 +1,185 @@
+"""CPU tests: the oracle (oracle/oracle_lz4.c) against the committed golden vectors produced by the
+UNMODIFIED reference (tests/golden/make_golden.py) and, where oracle/_ref is present, against the
+reference library itself.  This is what pins the oracle; the GPU parity tests then compare the CUDA
+path with the oracle."""
+import ctypes as C
+import random
+
+import pytest
+
+from conftest import OrcDesc, golden_bytes, orc_decode, ref_conduit_decode, gen_bytes
+
+
+def payload(man, name):
+    e = man[name]
+    return golden_bytes(e["raw"])[:e["size"]]
+
+
+def names(man):
+    return [k for k in man if not k.startswith("_")]
+
+
+def test_xxh32_known_answers(oracle, manifest):
+    kat = manifest["_xxh32_kat"]
+    assert kat[""] == 0x02CC5D05 and kat["abc"] == 0x32D153FF         # SURVEY.md appendix B (vendored xxhash.c)
+    assert oracle.orc_xxh32(b"", 0, 0) == kat[""]
+    assert oracle.orc_xxh32(b"abc", 3, 0) == kat["abc"]
+    assert oracle.orc_xxh32(b"hello" * 4, 20, 0) == kat["hello*4"]
+
+
+def test_xxh32_of_every_golden_file(oracle, manifest):
+    for name in names(manifest):
+        e = manifest[name]
+        d = payload(manifest, name)
+        assert oracle.orc_xxh32(d, len(d), 0) == e["xxh32"], name
+        for kind, fr in e["frames"].items():
+            b = golden_bytes(fr["file"])
+            assert len(b) == fr["size"] and oracle.orc_xxh32(b, len(b), 0) == fr["xxh32"], (name, kind)
+
+
+def test_golden_header_bytes(manifest):
+    # reference conduit defaults / lz4 -c -B4 -BX
+    assert manifest["numbers"]["frames"]["conduit"]["head"] == "04224d184040c0"
+    assert manifest["numbers"]["frames"]["cli_B4_BX"]["head"] == "04224d187440bd"
+    assert manifest["numbers"]["frames"]["cli"]["head"].startswith("04224d1864")
+
+
+def test_oracle_decodes_every_golden_frame(oracle, manifest):
+    for name in names(manifest):
+        d = payload(manifest, name)
+        for kind, fr in manifest[name]["frames"].items():
+            b = golden_bytes(fr["file"])
+            out, consumed = orc_decode(oracle, b, len(d) + 16)
+            assert out == d, (name, kind, out if isinstance(out, int) else len(out))
+            assert consumed == len(b), (name, kind)
+
+
+def test_oracle_frame_compress_matches_reference_frames(oracle, manifest):
+    """orc_frame_compress (independent blocks) must reproduce the reference library's bytes: the
+    cli_B4_BX frames are independent 64 KB blocks + both checksums made by the stock CLI."""
+    for name in names(manifest):
+        fr = manifest[name]["frames"].get("cli_B4_BX")
+        if fr is None:
+            continue
+        d = payload(manifest, name)
+        if len(d) < 65536:
+            continue        # single-read inputs go through LZ4F_compressFrame, which shrinks the block size id
+        desc = OrcDesc(4, 1, 1, 1, 0, 0, 0, 0)
+        cap = len(d) + len(d) // 200 + 1024
+        out = C.create_string_buffer(cap)
+        r = oracle.orc_frame_compress(d, len(d), out, cap, C.byref(desc))
+        assert r < (1 << 63)
+        assert out.raw[:r] == golden_bytes(fr["file"]), name
+
+
+def test_oracle_rejects_malformed_blocks(oracle):
+    out = C.create_string_buffer(256)
+    # lz4/tests/fuzzer.c:1040-1053: this 17-byte input must be rejected
+    bad = bytes([0xEE]) + bytes(14) + bytes([0x0E, 0x00])
+    assert oracle.orc_block_decompress(bad, len(bad), out, 256, 0) < 0
+    assert oracle.orc_block_decompress(b"\xff", 1, out, 256, 0) < 0
+    assert oracle.orc_block_decompress(b"", 0, out, 256, 0) < 0
+    assert oracle.orc_block_decompress(b"\x00", 1, out, 256, 0) == 0
+
+
+# ---------------------------------------------------------------- against the live reference library
+def test_block_compressor_byte_exact_vs_reference(oracle, ref, gen):
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    rnd = random.Random(1)
+    cases = [gen_bytes(gen, "loglike", n) for n in (13, 100, 4096, 65535 + 11, 65536 + 11, 300000)]
+    cases += [gen_bytes(gen, "textlike", 200000), bytes(100000), gen_bytes(gen, "random", 5000),
+              bytes(rnd.getrandbits(2) for _ in range(50000))]
+    # lz4/tests/fuzzer.c:1079-1087: 65 KB of noise with the first 267 bytes zeroed compresses to size-1... (shape only)
+    cases.append(bytes(267) + gen_bytes(gen, "random", 65 * 1024 - 267))
+    for d in cases:
+        cap = len(d) + len(d) // 255 + 32
+        a, b = C.create_string_buffer(cap), C.create_string_buffer(cap)
+        ra = oracle.orc_block_compress(d, len(d), a, cap)
+        rb = ref.LZ4_compress_default(d, b, len(d), cap)
+        assert ra == rb and a.raw[:ra] == b.raw[:rb], len(d)
+        back = C.create_string_buffer(len(d) + 1)
+        assert oracle.orc_block_decompress(a.raw[:ra], ra, back, len(d), 0) == len(d)
+        assert back.raw[:len(d)] == d
+
+
+def test_block_decoder_matches_reference_on_noise(oracle, ref, gen):
+    """Decode-garbage robustness (lz4/tests/frametest.c:1044-1073 idea): corrupt valid blocks; oracle and
+    reference must agree on accept/reject and on the bytes when both accept."""
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    rnd = random.Random(2)
+    d = gen_bytes(gen, "loglike", 20000)
+    cap = len(d) + 256
+    comp = C.create_string_buffer(cap)
+    n = ref.LZ4_compress_default(d, comp, len(d), cap)
+    good = comp.raw[:n]
+    agree = 0
+    for _ in range(400):
+        b = bytearray(good)
+        for _ in range(rnd.randint(1, 3)):
+            b[rnd.randrange(len(b))] = rnd.getrandbits(8)
+        if rnd.random() < 0.3:
+            b = b[:rnd.randrange(1, len(b))]
+        b = bytes(b)
+        o1, o2 = C.create_string_buffer(len(d) + 64), C.create_string_buffer(len(d) + 64)
+        r1 = oracle.orc_block_decompress(b, len(b), o1, len(d), 0)
+        r2 = ref.LZ4_decompress_safe(b, o2, len(b), len(d))
+        if r1 >= 0 and r2 >= 0:
+            assert r1 == r2 and o1.raw[:r1] == o2.raw[:r2]
+            agree += 1
+        else:
+            # documented deviation: offset 0 is rejected by the oracle, accepted by v1.9.2 (oracle_lz4.c)
+            assert (r1 < 0) == (r2 < 0) or (r1 < 0 and r2 >= 0), (r1, r2)
+    assert agree > 0
+
+
+def test_conduit_replay_is_chunking_independent(ref, gen):
+    """the reference conduit's output does not depend on how the input is chunked."""
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    d = gen_bytes(gen, "loglike", 300000)
+    cap = len(d) + 70000
+    outs = []
+    for chunk in (0, 1000, 16384, 100000):
+        o = C.create_string_buffer(cap)
+        r = ref.ref_conduit_compress(d, len(d), o, cap, chunk, 0)
+        assert not ref.LZ4F_isError(r)
+        outs.append(o.raw[:r])
+    o = C.create_string_buffer(cap)
+    r = ref.ref_conduit_compress_yi(d, len(d), o, cap, 50000)
+    outs.append(o.raw[:r])
+    assert all(x == outs[0] for x in outs)
+    assert outs[0][:7].hex() == "04224d184040c0"
+    back, consumed = ref_conduit_decode(ref, outs[0], len(d) + 16, chunk=777)
+    assert back == d and consumed == len(outs[0])
+
+
+def test_oracle_frame_decoder_vs_reference_conduit(oracle, ref, gen):
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    d = gen_bytes(gen, "loglike", 500000) + bytes(70000) + gen_bytes(gen, "random", 70000)
+    cap = len(d) + 70000
+    for (bsid, indep, cc, bc, cs, chunk) in [(4, 0, 1, 1, 0, 65536), (5, 1, 0, 0, 1, 0), (7, 1, 1, 0, 0, 4 << 20),
+                                             (4, 0, 0, 0, 0, 30000), (6, 0, 1, 0, 0, 100000)]:
+        o = C.create_string_buffer(cap)
+        r = ref.ref_frame_compress(d, len(d), o, cap, bsid, indep, cc, bc, cs, 1, chunk)
+        assert not ref.LZ4F_isError(r)
+        fr = o.raw[:r]
+        a, ca = orc_decode(oracle, fr, len(d) + 16)
+        b, cb = ref_conduit_decode(ref, fr, len(d) + 16, chunk=4096)
+        assert a == d and b == d and ca == cb == len(fr)
+        # corrupt one byte in the middle: both must reject
+        bad = bytearray(fr); bad[len(bad) // 2] ^= 0x5A; bad = bytes(bad)
+        a, _ = orc_decode(oracle, bad, len(d) + 16)
+        b, _ = ref_conduit_decode(ref, bad, len(d) + 16)
+        if cc or bc:
+            assert isinstance(a, int) and isinstance(b, int)
+
+
+def test_xxh32_streaming_vs_reference(oracle, ref, gen):
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    d = gen_bytes(gen, "random", 100003)
+    for n in (0, 1, 15, 16, 17, 31, 32, 33, 1000, 100003):
+        assert oracle.orc_xxh32(d, n, 0) == ref.ref_xxh32(d, n, 0) == ref.ref_xxh32_stream(d, n, 0, 7)
