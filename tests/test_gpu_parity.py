@@ -167,7 +167,9 @@ def roundtrip_everywhere(codec, oracle, ref, lz4_cli, d, prefs, tmp_path=None):
     # (3) the reference conduit replay (16 KB output slices, odd input chunking)
     if ref is not None:
         got, rc = ref_conduit_decode(ref, fr, len(d) + 16, chunk=10007)
-        assert got == d and rc == consumed2
+        # within one ByteString the reference keeps feeding LZ4F_decompress after the EndMark (Conduit.hsc:681-684),
+        # so a trailing skippable index frame in the same chunk is skipped and counted as consumed
+        assert got == d and rc in (consumed2, consumed)
     # (4) the stock CLI (skips our trailing skippable index frame, lz4io.c:1094-1135)
     if lz4_cli is not None:
         if codec.prefs.write_index:          # a file: the v1.9.2 CLI skips skippable frames with fseek (lz4io.c:1124-1133)
