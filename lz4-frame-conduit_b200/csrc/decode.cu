@@ -204,89 +204,200 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
 // All lanes keep identical parse state (uniform control flow); literal and match copies are spread
 // over the 32 lanes.  Acceptance rules mirror the reference decoder's safe loop (lz4.c:1844-2055).
 // ------------------------------------------------------------------------------------------------
-struct Cursor {            // what the warp knows about the piece it is decoding
-    const uint8_t* src;    // compressed buffer base
-    uint8_t* dst;          // output buffer base
-    uint64_t ip, iend;     // current / end of this piece's compressed bytes
-    uint64_t iend_blk;     // end of the owning block's compressed bytes (reference's `iend`)
-    uint64_t op, oend;     // current output position / output limit of the owning block (reference's `oend`)
-    uint64_t opiece_end;   // exact end of this piece's output (PIECE_EXACT) or == oend
-    uint64_t low;          // lowest output offset a match may read (window start)
+struct Cursor {            // what the warp knows about the piece it is decoding (all offsets 32-bit, block-relative)
+    const uint8_t* sp;     // first compressed byte of the owning block
+    uint8_t* dp;           // first output byte of the owning block
+    uint32_t ip, iend;     // current / end of this piece's compressed bytes
+    uint32_t iend_blk;     // end of the owning block's compressed bytes (reference's `iend`)
+    uint32_t op, oend;     // current output position / output limit of the owning block (reference's `oend`)
+    uint32_t opiece_end;   // exact end of this piece's output (PIECE_EXACT) or == oend
+    uint32_t reach;        // a match at output position m may reach back `m + reach` bytes (mod 2^32):
+                           // independent piece: -piece_start;  linked: bytes of earlier output in front of the block
 };
 
+// Per-lane byte copy of n bytes; loads are batched four at a time ahead of the stores so that a lane
+// keeps several loads in flight.  `s` must not overlap the destination (callers guarantee it).
+__device__ __forceinline__ void lane_copy(uint8_t* d, const uint8_t* s, uint32_t n) {
+    uint32_t k = 0;
+    for (; k + 4 <= n; k += 4) {
+        uint8_t a = s[k], b = s[k + 1], c = s[k + 2], e = s[k + 3];
+        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
+    }
+    for (; k < n; ++k) d[k] = s[k];
+}
+
+// Per-lane match copy: replicates the FINAL window [d - off, d) with period `off` (off >= n: plain copy).
+// All loads come from the window, never from bytes this call writes, so they do not wait on the stores.
+__device__ __forceinline__ void lane_match(uint8_t* d, uint32_t off, uint32_t n) {
+    const uint8_t* s = d - off;
+    uint32_t r = 0, k = 0;
+    for (; k + 4 <= n; k += 4) {
+        uint8_t a = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        uint8_t b = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        uint8_t c = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        uint8_t e = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
+    }
+    for (; k < n; ++k) { d[k] = s[r]; r = (r + 1 == off) ? 0u : r + 1; }
+}
+
+// Warp-cooperative match copy (long matches): the source window [d - off, d) is final.
+__device__ __forceinline__ void warp_match(uint8_t* d, uint32_t offset, uint64_t ml, uint32_t lane) {
+    const uint8_t* m = d - offset;
+    if (offset >= ml) {
+        group_copy(d, m, ml, lane, 32);
+    } else if (offset >= 32) {
+        for (uint64_t i = lane; i < ml; i += 32) d[i] = m[i % offset];
+    } else {
+        // short period, long run: each lane owns byte positions i = lane + 32k; its index inside the
+        // pattern advances by 32 mod offset every step.  Bulk part as 4-byte words once 4-aligned.
+        uint32_t r = lane % offset, step = 32u % offset;
+        for (uint64_t i = lane; i < ml; i += 32) {
+            d[i] = m[r];
+            r += step; if (r >= offset) r -= offset;
+        }
+    }
+}
+
+constexpr uint32_t LANE_CAP = 32;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
+
+// Decodes one piece.  The warp first WALKS up to 32 sequences (uniform control flow: every lane follows the
+// token chain, lane i keeps the fields of sequence i), then copies them lane-parallel: literals of all 32
+// sequences at once, then matches in rounds — a match may run as soon as every byte it reads is final, i.e.
+// lies below the destination of the first match still pending (all literals are already in place).
+// The walk has a short path for the common sequence (both nibbles < 15, far from every limit) whose only
+// check is the offset; everything else takes the general path with the reference's acceptance rules.
 // returns 0 or an Err; c.op is advanced
-__device__ __forceinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
+__device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
 {
     const uint32_t lane = lane_id();
-    const uint8_t* __restrict__ src = c.src;
-    uint8_t* dst = c.dst;
-    uint64_t ip = c.ip, op = c.op;
-    const uint64_t iend = c.iend_blk;
+    const uint8_t* __restrict__ sp = c.sp;
+    uint8_t* dp = c.dp;
+    uint32_t ip = c.ip, op = c.op;
+    const uint32_t iend = c.iend_blk, pend = c.iend, oend = c.oend, opend = c.opiece_end, reach = c.reach;
+    // short path (lengths with at most one extension byte) allowed while  ip + 288 <= pend  and
+    // op + 560 <= min(oend, opend): inside that region none of the general path's limit checks can fire
+    uint32_t i_fast = pend >= 288u ? pend - 287u : 0u;
+    const uint32_t olim = oend < opend ? oend : opend;
+    uint32_t o_fast = olim >= 560u ? olim - 559u : 0u;
+    asm volatile("" : "+r"(i_fast), "+r"(o_fast));                          // keep them in registers (no re-derivation per sequence)
     uint32_t err = 0;
-    if (c.iend == ip) return E_decompressionFailed;                         // empty input (lz4.c:1702)
-    for (;;) {
-        if (ip >= c.iend) { err = E_decompressionFailed; break; }
-        uint32_t token = src[ip++];
-        uint64_t ll = token >> 4;
-        if (ll == 15) {                                                     // lz4.c:1882-1889
-            if (ip + 15 >= iend) { err = E_decompressionFailed; break; }
-            uint32_t sbyte;
-            do { sbyte = src[ip++]; ll += sbyte; if (ip + 15 >= iend) break; } while (sbyte == 255);
-        }
-        // last-sequence test (lz4.c:1906): not enough input for an offset + next token, or the
-        // literals reach the last 12 bytes of the block's output window
-        bool last = (op + ll + 12 > c.oend) || (ip + ll + 8 > iend);
-        if (last) {
-            if (ip + ll != iend || op + ll > c.oend || !ends_block || op + ll > c.opiece_end || iend != c.iend) {
-                err = E_decompressionFailed; break;
-            }
-        } else if (ip + ll + 2 > c.iend || op + ll > c.opiece_end) { err = E_decompressionFailed; break; }
-        // literals
-        {
-            const uint8_t* s = src + ip; uint8_t* d = dst + op;
-            if (ll <= 32) { if (lane < ll) d[lane] = s[lane]; }
-            else group_copy(d, s, ll, lane, 32);
-        }
-        ip += ll; op += ll;
-        if (last) break;
-        uint32_t offset = (uint32_t)src[ip] | ((uint32_t)src[ip + 1] << 8);
-        ip += 2;
-        uint64_t ml = token & 15u;
-        if (ml == 15) {                                                     // lz4.c:1967-1972
-            uint32_t sbyte; bool bad = false;
-            do { sbyte = src[ip++]; ml += sbyte; if (ip + 4 >= iend) { bad = true; break; } } while (sbyte == 255);
-            if (bad) { err = E_decompressionFailed; break; }
-        }
-        ml += 4;
-        if (offset == 0 || (uint64_t)offset > op - c.low) { err = E_decompressionFailed; break; }   // lz4.c:1977
-        if (op + ml + 5 > c.oend || op + ml > c.opiece_end) { err = E_decompressionFailed; break; }   // lz4.c:2033-2035
-        // match copy: the source window [op-offset, op) is final (earlier sequences of this chain);
-        // overlapping matches replicate it with period `offset`.
-        __syncwarp();
-        {
-            uint8_t* d = dst + op;
-            const uint8_t* m = d - offset;
-            if (offset >= ml) {
-                if (ml <= 32) { if (lane < ml) d[lane] = m[lane]; }
-                else group_copy(d, m, ml, lane, 32);
-            } else if (offset >= 32 || ml <= 32) {
-                // period >= 32 or short: lane i copies i, i+32, ... from inside the final window
-                for (uint64_t i = lane; i < ml; i += 32) d[i] = m[i % offset];
-            } else {
-                // short period, long run (offset < 32 < ml): each lane owns byte positions i = lane + 32k;
-                // its source index inside the pattern advances by 32 mod offset every step.
-                uint32_t r = lane % offset, step = 32u % offset;
-                for (uint64_t i = lane; i < ml; i += 32) {
-                    d[i] = m[r];
-                    r += step; if (r >= offset) r -= offset;
+    if (pend == ip) return E_decompressionFailed;                           // empty input (lz4.c:1702)
+    bool finished = false;
+    while (!finished) {
+        uint32_t my_a = 0, my_b = 0, my_lit = 0, my_ll = 0, my_ml = 0, my_off = 1;
+        bool my_packed = true;
+        const uint32_t op0 = op;
+        uint32_t n = 0;
+        for (; n < 32; ++n) {
+            if (ip < i_fast && op < o_fast) {
+                const uint32_t token = sp[ip];
+                uint32_t ll = token >> 4, ml = (token & 15u) + 4u, lit = ip + 1u;
+                bool more = false;
+                if (ll == 15u) { const uint32_t e = sp[lit++]; ll += e; more = (e == 255u); }
+                uint32_t q = lit + ll;
+                const uint32_t offset = (uint32_t)sp[q] | ((uint32_t)sp[q + 1] << 8);
+                q += 2u;
+                if (ml == 19u) { const uint32_t e = sp[q++]; ml += e; more |= (e == 255u); }
+                if (!more) {
+                    const uint32_t mop = op + ll;
+                    if (offset == 0u || offset > mop + reach) { err = E_decompressionFailed; break; }   // lz4.c:1977
+                    if (lane == n) { my_a = lit | (ll << 22); my_b = offset | (ml << 16); }
+                    ip = q;
+                    op = mop + ml;
+                    continue;
                 }
             }
+            // ---- general path
+            if (ip >= pend) { err = E_decompressionFailed; break; }
+            const uint32_t token = sp[ip++];
+            uint32_t ll = token >> 4;
+            if (ll == 15u) {                                                // lz4.c:1882-1889
+                if (ip + 15u >= iend) { err = E_decompressionFailed; break; }
+                uint32_t sbyte;
+                do { sbyte = sp[ip++]; ll += sbyte; if (ip + 15u >= iend) break; } while (sbyte == 255u);
+            }
+            // last-sequence test (lz4.c:1906): not enough input for an offset + next token, or the
+            // literals reach the last 12 bytes of the block's output window.  (ll <= 255 * 4 MB: no overflow)
+            const bool last = (op + ll + 12u > oend) || (ip + ll + 8u > iend);
+            if (last) {
+                if (ip + ll != iend || op + ll > oend || !ends_block || op + ll > opend || iend != pend) {
+                    err = E_decompressionFailed; break;
+                }
+                if (lane == n) { my_lit = ip; my_ll = ll; my_ml = 0; my_packed = false; }
+                ip += ll; op += ll; ++n; finished = true;
+                break;
+            }
+            if (ip + ll + 2u > pend || op + ll > opend) { err = E_decompressionFailed; break; }
+            const uint32_t lit = ip;
+            ip += ll;
+            const uint32_t offset = (uint32_t)sp[ip] | ((uint32_t)sp[ip + 1] << 8);
+            ip += 2u;
+            uint32_t ml = token & 15u;
+            if (ml == 15u) {                                                // lz4.c:1967-1972
+                uint32_t sbyte; bool bad = false;
+                do { sbyte = sp[ip++]; ml += sbyte; if (ip + 4u >= iend) { bad = true; break; } } while (sbyte == 255u);
+                if (bad) { err = E_decompressionFailed; break; }
+            }
+            ml += 4u;
+            const uint32_t mop = op + ll;
+            if (offset == 0u || offset > mop + reach) { err = E_decompressionFailed; break; }           // lz4.c:1977
+            if ((uint64_t)mop + ml + 5u > oend || (uint64_t)mop + ml > opend) { err = E_decompressionFailed; break; } // lz4.c:2033-2035
+            if (lane == n) { my_lit = lit; my_ll = ll; my_ml = ml; my_off = offset; my_packed = false; }
+            op = mop + ml;
+            if (ip == pend && !ends_block) {                                // sub-block ends after a match
+                if (op != opend) err = E_decompressionFailed;
+                ++n; finished = true;
+                break;
+            }
+        }
+        if (err) break;                                                     // nothing of a bad batch is copied
+        if (my_packed) { my_lit = my_a & 0x3FFFFFu; my_ll = my_a >> 22; my_off = my_b & 0xFFFFu; my_ml = my_b >> 16; }
+        // output position of sequence i = op0 + sum of the sizes of the sequences before it
+        uint32_t my_op;
+        {
+            const uint32_t sz = my_ll + my_ml;
+            uint32_t x = sz;
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, x, d); if ((int)lane >= d) x += y; }
+            my_op = op0 + x - sz;
+        }
+
+        // ---- literals: lane i copies the literals of sequence i; long runs use the whole warp
+        {
+            const bool act = lane < n && my_ll != 0;
+            if (act && my_ll <= LANE_CAP) lane_copy(dp + my_op, sp + my_lit, my_ll);
+            uint32_t longm = __ballot_sync(FULL_MASK, act && my_ll > LANE_CAP);
+            while (longm) {
+                const int j = __ffs(longm) - 1; longm &= longm - 1;
+                const uint32_t l = __shfl_sync(FULL_MASK, my_lit, j), o = __shfl_sync(FULL_MASK, my_op, j);
+                const uint32_t len = __shfl_sync(FULL_MASK, my_ll, j);
+                group_copy(dp + o, sp + l, len, lane, 32);
+            }
         }
         __syncwarp();
-        op += ml;
-        if (ip == c.iend && !ends_block) {                                  // sub-block ends after a match
-            if (op != c.opiece_end) err = E_decompressionFailed;
-            break;
+        // ---- matches, in rounds
+        {
+            const uint32_t my_mop = my_op + my_ll;
+            // end of the bytes read, relative to the match destination: -(off) + min(ml, off)  (<= 0)
+            const int32_t my_need = (int32_t)(my_ml < my_off ? my_ml : my_off) - (int32_t)my_off;
+            uint32_t pending = __ballot_sync(FULL_MASK, lane < n && my_ml != 0);
+            while (pending) {
+                const int f = __ffs(pending) - 1;
+                const uint32_t W = __shfl_sync(FULL_MASK, my_mop, f);       // everything below W is final
+                const uint32_t ml_f = __shfl_sync(FULL_MASK, my_ml, f);
+                if (ml_f > LANE_CAP) {
+                    const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
+                    warp_match(dp + W, off_f, ml_f, lane);
+                    pending &= ~(1u << f);
+                } else {
+                    const bool ready = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
+                                       ((int)lane == f || (int64_t)my_mop + my_need <= (int64_t)W);
+                    if (ready) lane_match(dp + my_mop, my_off, my_ml);
+                    pending &= ~__ballot_sync(FULL_MASK, ready);
+                }
+                __syncwarp();
+            }
         }
     }
     c.ip = ip; c.op = op;
@@ -331,19 +442,24 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
                 }
             } else {
                 Cursor cu;
-                cu.src = src; cu.dst = dst;
-                cu.ip = pc.src_off; cu.iend = pc.src_off + pc.src_len;
-                cu.iend_blk = br.src_off + br.csize;
-                cu.op = op; cu.oend = oend;
-                cu.opiece_end = (pc.flags & PIECE_EXACT) ? op + pc.dst_len : oend;
+                cu.sp = src + br.src_off; cu.dp = dst + blk_out;
+                cu.ip = (uint32_t)(pc.src_off - br.src_off); cu.iend = cu.ip + pc.src_len;
+                cu.iend_blk = br.csize;
+                const uint32_t op_rel = (uint32_t)(op - blk_out);
+                const uint32_t ocap = (uint32_t)(oend - blk_out);
+                cu.op = op_rel; cu.oend = ocap;
+                cu.opiece_end = (pc.flags & PIECE_EXACT) ? op_rel + pc.dst_len : ocap;
+                if (cu.opiece_end > ocap && !(pc.flags & PIECE_EXACT)) cu.opiece_end = ocap;
                 // window start: independent blocks/sub-blocks may only reference their own output;
                 // linked blocks reach up to 64 KB into the earlier output of the chain (lz4frame.c:1286-1349)
-                cu.low = linked ? chain_start : op;
+                if (linked) { uint64_t h = blk_out - chain_start; cu.reach = h > 0x40000000ull ? 0x40000000u : (uint32_t)h; }
+                else cu.reach = 0u - op_rel;
                 uint32_t e = decode_piece(cu, (pc.flags & PIECE_ENDS_BLOCK) != 0);
-                if ((pc.flags & PIECE_EXACT) && e == 0 && cu.op - op != pc.dst_len) e = E_decompressionFailed;
-                if (e && oend - blk_out < block_size) e = E_dstMaxSize_tooSmall;   // ran out of destination
-                po.err = e; po.out_len = (uint32_t)(cu.op - op);
-                op = cu.op;
+                const uint32_t produced = cu.op - op_rel;
+                if ((pc.flags & PIECE_EXACT) && e == 0 && produced != pc.dst_len) e = E_decompressionFailed;
+                if (e && ocap < block_size) e = E_dstMaxSize_tooSmall;          // ran out of destination
+                po.err = e; po.out_len = produced;
+                op += produced;
             }
             if (po.err) dead = true;
             if (lane == 0) outs[pi] = po;

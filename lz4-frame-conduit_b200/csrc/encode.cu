@@ -36,22 +36,63 @@ __device__ __forceinline__ uint32_t put_len_ext(uint8_t* out, uint32_t o, uint32
     return o + n255 + 1u;
 }
 
-// One sequence: token, literal length bytes, literals, offset, match length bytes (lz4_Block_format.md:27-105)
-__device__ __forceinline__ uint32_t emit_sequence(uint8_t* out, uint32_t o, const uint8_t* lit, uint32_t ll,
-                                                  uint32_t off, uint32_t mlc, uint32_t lane) {
-    if (lane == 0) out[o] = (uint8_t)(((ll < 15u ? ll : 15u) << 4) | (mlc < 15u ? mlc : 15u));
-    o = put_len_ext(out, o + 1, ll, lane);
-    if (ll <= 32) { if (lane < ll) out[o + lane] = lit[lane]; }
-    else group_copy(out + o, lit, ll, lane, 32);
-    o += ll;
-    if (lane == 0) { out[o] = (uint8_t)off; out[o + 1] = (uint8_t)(off >> 8); }
-    return put_len_ext(out, o + 2, mlc, lane);
+constexpr uint32_t ENC_LANE_CAP = 32;     // literal runs up to this many bytes are copied one-lane-per-sequence
+
+// Up to 32 parsed sequences wait here, one per lane, until the batch is written out.
+struct Pending { uint32_t anchor, ll, off, mlc; };
+
+// Writes `npend` sequences (lane i holds sequence i) at out + o: token, literal-length bytes, literals, offset,
+// match-length bytes (lz4_Block_format.md:27-105).  Sizes are prefix-summed so every lane writes its own
+// sequence; only literal runs longer than ENC_LANE_CAP are copied by the whole warp.  Returns the new o.
+__device__ __forceinline__ uint32_t emit_batch(uint8_t* __restrict__ out, uint32_t o, const uint8_t* __restrict__ base,
+                                               uint32_t npend, const Pending& pd, uint32_t lane)
+{
+    const bool act = lane < npend;
+    const uint32_t hdr = 1u + len_bytes(pd.ll);
+    const uint32_t sz = act ? hdr + pd.ll + 2u + len_bytes(pd.mlc) : 0u;
+    uint32_t x = sz;
+    #pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, x, d); if ((int)lane >= d) x += y; }
+    const uint32_t my_o = o + x - sz;
+    const uint32_t total = __shfl_sync(FULL_MASK, x, 31);
+    if (act) {
+        uint8_t* w = out + my_o;
+        *w++ = (uint8_t)(((pd.ll < 15u ? pd.ll : 15u) << 4) | (pd.mlc < 15u ? pd.mlc : 15u));
+        if (pd.ll >= 15u) { uint32_t r = pd.ll - 15u; while (r >= 255u) { *w++ = 255; r -= 255u; } *w++ = (uint8_t)r; }
+        if (pd.ll <= ENC_LANE_CAP) {
+            const uint8_t* l = base + pd.anchor;
+            uint32_t k = 0;
+            for (; k + 4 <= pd.ll; k += 4) { uint8_t a = l[k], b = l[k + 1], c = l[k + 2], e = l[k + 3]; w[k] = a; w[k + 1] = b; w[k + 2] = c; w[k + 3] = e; }
+            for (; k < pd.ll; ++k) w[k] = l[k];
+        }
+        w += pd.ll;
+        w[0] = (uint8_t)pd.off; w[1] = (uint8_t)(pd.off >> 8); w += 2;
+        if (pd.mlc >= 15u) { uint32_t r = pd.mlc - 15u; while (r >= 255u) { *w++ = 255; r -= 255u; } *w++ = (uint8_t)r; }
+    }
+    uint32_t longm = __ballot_sync(FULL_MASK, act && pd.ll > ENC_LANE_CAP);
+    while (longm) {
+        const int j = __ffs(longm) - 1; longm &= longm - 1;
+        const uint32_t a = __shfl_sync(FULL_MASK, pd.anchor, j), l = __shfl_sync(FULL_MASK, pd.ll, j);
+        const uint32_t at = __shfl_sync(FULL_MASK, my_o + hdr, j);
+        group_copy(out + at, base + a, l, lane, 32);
+    }
+    return o + total;
 }
 
 // ------------------------------------------------------------------------------------------------
-// match finder + emitter: one warp per independent sub-block.
+// match finder + emitter: one warp per independent sub-block, 128 positions per step.
+//   1. probe   every lane hashes 4 positions and reads their table entries (all 128 look-ups happen before
+//              any insert of the step, so 128 candidate loads are in flight together)
+//   2. verify  4-byte compare at the candidates -> a 128-bit hit map (4 ballots)
+//   3. select  greedy, in position order: first hit at or after the parse position, extended backwards
+//              to the pending literals and forwards as far as it goes (warp-wide compares); the sequence
+//              is parked in a lane (Pending) and written out 32 at a time (emit_batch)
+//   4. insert  positions that did not end up inside a match go into the table (inserting match
+//              interiors would evict the field starts the following lines need)
+// After a step without a hit the probe stride doubles (1, 2, 4, 8 bytes), as incompressible data should
+// cost little; a hit resets it.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(ENC_WARPS * 32)
+__global__ void __launch_bounds__(ENC_WARPS * 32, 3)
 find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restrict__ scratch,
                  SubOut* __restrict__ subs, uint32_t* __restrict__ ticket)
 {
@@ -87,74 +128,115 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
         }
         const uint32_t matchlimit = (usize >= 5u) ? ((b1 < usize - 5u) ? b1 : usize - 5u) : 0u;
 
-        uint32_t ip = b0, anchor = b0, o = 0;
-        uint32_t miss = 0, nseq = 0, first_ll = 0, first_hdr = 0;
+        uint32_t ip = b0, anchor = b0, o = 0, T0 = b0;
+        uint32_t miss = 0, nseq = 0, first_ll = 0, first_hdr = 0, npend = 0;
+        Pending pd = {0, 0, 0, 0};
 
-        while (ip < limit) {
-            const uint32_t sl = (miss >> 2) < 3u ? (miss >> 2) : 3u;          // probe stride 1,2,4,8 after misses
-            const uint32_t p = ip + (lane << sl);
-            const bool valid = p < limit;
-            uint32_t v = 0, h = 0, rel = p - b0;
-            int32_t c = -1;
-            bool hit = false;
-            if (valid) {
-                v = ld32u(base + p);
-                h = hash4(v);
-                uint32_t cl = tab[h];
-                c = (int32_t)((rel & ~0xFFFFu) | cl);
-                if ((uint32_t)c >= rel) c -= 65536;
-                if (c >= 0 && rel - (uint32_t)c < 65536u) hit = (ld32u(base + b0 + c) == v);
+        while (T0 < limit) {
+            const uint32_t sl = miss < 3u ? miss : 3u;                        // probe stride 1, 2, 4, 8
+            // ---- 1. probe
+            uint32_t v[4], h[4], rel[4]; int32_t c[4]; bool ok[4];
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t p = T0 + ((32u * k + lane) << sl);
+                ok[k] = p < limit;
+                rel[k] = p - b0;
+                v[k] = ok[k] ? ld32u(base + p) : 0u;
+                h[k] = hash4(v[k]);
             }
-            const uint32_t m = __ballot_sync(FULL_MASK, hit);
-            const int f = __ffs(m) - 1;                                       // -1 when no lane hit
-            // insert only the positions up to the match start: positions inside the match would evict the
-            // entries (field starts) that the following lines need — worth 40 % of ratio on log-like data
-            if (valid && (m == 0 || (int)lane <= f)) tab[h] = (uint16_t)rel;
-            __syncwarp();
-            if (m == 0) { ip += 32u << sl; ++miss; continue; }
-            miss = 0;
-            uint32_t mpos = __shfl_sync(FULL_MASK, p, f);
-            uint32_t cpos = b0 + (uint32_t)__shfl_sync(FULL_MASK, c, f);
-            // backward extension (up to 32 bytes), bounded by the pending literals and the sub-block start
-            {
-                uint32_t mb = mpos - anchor, cb = cpos - b0;
-                uint32_t maxback = mb < cb ? mb : cb;
-                bool eq = lane < maxback && base[mpos - 1 - lane] == base[cpos - 1 - lane];
-                uint32_t ne = __ballot_sync(FULL_MASK, !eq);
-                uint32_t back = ne ? (uint32_t)(__ffs(ne) - 1) : 32u;
-                mpos -= back; cpos -= back;
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t cl = tab[h[k]];
+                int32_t cc = (int32_t)((rel[k] & ~0xFFFFu) | cl);
+                if ((uint32_t)cc >= rel[k]) cc -= 65536;
+                c[k] = cc;
             }
-            // forward extension: every lane compares 4 bytes; bytes at and after matchlimit never count
-            uint32_t len = 0;
-            for (;;) {
-                const uint32_t q = mpos + len + lane * 4u;
-                uint32_t avail = matchlimit > q ? matchlimit - q : 0u;
-                uint32_t nbytes = 0;
-                if (avail) {
-                    uint32_t x = ld32u(base + q) ^ ld32u(base + cpos + len + lane * 4u);
-                    nbytes = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4u;
-                    if (nbytes > avail) nbytes = avail;
+            // ---- 2. verify
+            uint32_t H[4];
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                bool hit = false;
+                if (ok[k] && c[k] >= 0 && rel[k] - (uint32_t)c[k] < 65536u) hit = (ld32u(base + b0 + c[k]) == v[k]);
+                H[k] = __ballot_sync(FULL_MASK, hit);
+            }
+            const uint32_t span = 128u << sl;
+            uint32_t C0 = 0, C1 = 0, C2 = 0, C3 = 0;                          // sample indices swallowed by a match
+            if ((H[0] | H[1] | H[2] | H[3]) != 0u) {
+                miss = 0;
+                // ---- 3. select
+                uint32_t q = 0;                                               // next sample index to consider
+                while (q < 128u) {
+                    uint32_t kq = q >> 5, m;
+                    m = (kq == 0 ? H[0] : kq == 1 ? H[1] : kq == 2 ? H[2] : H[3]) & (0xFFFFFFFFu << (q & 31u));
+                    while (m == 0u && ++kq < 4u) m = (kq == 1 ? H[1] : kq == 2 ? H[2] : H[3]);
+                    if (m == 0u) break;
+                    const uint32_t ln = (uint32_t)__ffs(m) - 1u, idx = kq * 32u + ln;
+                    const int32_t csel = kq == 0 ? c[0] : kq == 1 ? c[1] : kq == 2 ? c[2] : c[3];
+                    uint32_t mpos = T0 + (idx << sl);
+                    uint32_t cpos = b0 + (uint32_t)__shfl_sync(FULL_MASK, csel, ln);
+                    // backward extension (up to 32 bytes), bounded by the pending literals and the sub-block start
+                    {
+                        const uint32_t mb = mpos - anchor, cb = cpos - b0;
+                        const uint32_t maxback = mb < cb ? mb : cb;
+                        const bool eq = lane < maxback && base[mpos - 1 - lane] == base[cpos - 1 - lane];
+                        const uint32_t ne = __ballot_sync(FULL_MASK, !eq);
+                        const uint32_t back = ne ? (uint32_t)(__ffs(ne) - 1) : 32u;
+                        mpos -= back; cpos -= back;
+                    }
+                    // forward extension: every lane compares 4 bytes; bytes at and after matchlimit never count
+                    uint32_t len = 0;
+                    for (;;) {
+                        const uint32_t qq = mpos + len + lane * 4u;
+                        const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
+                        uint32_t nbytes = 0;
+                        if (avail) {
+                            const uint32_t xx = ld32u(base + qq) ^ ld32u(base + cpos + len + lane * 4u);
+                            nbytes = xx ? (uint32_t)(__ffs(xx) - 1) >> 3 : 4u;
+                            if (nbytes > avail) nbytes = avail;
+                        }
+                        const uint32_t part = __ballot_sync(FULL_MASK, nbytes != 4u);
+                        if (part == 0) { len += 128u; continue; }
+                        const int g = __ffs(part) - 1;
+                        len += (uint32_t)g * 4u + __shfl_sync(FULL_MASK, nbytes, g);
+                        break;
+                    }
+                    if (len < 4u) { q = idx + 1u; continue; }                 // guard: never emit an invalid match
+                    if (lane == npend) { pd.anchor = anchor; pd.ll = mpos - anchor; pd.off = mpos - cpos; pd.mlc = len - 4u; }
+                    ++npend;
+                    const uint32_t mend = mpos + len;
+                    anchor = ip = mend;
+                    // sample indices strictly inside the match: ((mpos - T0) >> sl) + 1 .. first index at or after mend
+                    const uint32_t j0 = mpos >= T0 ? ((mpos - T0) >> sl) + 1u : 0u;
+                    uint32_t j1 = (mend - T0 + (1u << sl) - 1u) >> sl; if (j1 > 128u) j1 = 128u;
+                    if (j1 > j0) {
+                        #define B2_RANGE(lo, hi, w) { uint32_t a_ = lo > 32u * w ? lo - 32u * w : 0u, b_ = hi > 32u * w ? hi - 32u * w : 0u; \
+                            if (a_ < 32u && b_ > a_) { uint32_t mk = 0xFFFFFFFFu << a_; if (b_ < 32u) mk &= ~(0xFFFFFFFFu << b_); C##w |= mk; } }
+                        B2_RANGE(j0, j1, 0) B2_RANGE(j0, j1, 1) B2_RANGE(j0, j1, 2) B2_RANGE(j0, j1, 3)
+                        #undef B2_RANGE
+                    }
+                    q = j1;
+                    if (npend == 32u) {
+                        if (nseq == 0) { first_ll = __shfl_sync(FULL_MASK, pd.ll, 0); first_hdr = 1u + len_bytes(first_ll); }
+                        o = emit_batch(out, o, base, npend, pd, lane);
+                        nseq += npend; npend = 0;
+                    }
                 }
-                const uint32_t part = __ballot_sync(FULL_MASK, nbytes != 4u);
-                if (part == 0) { len += 128u; continue; }
-                const int g = __ffs(part) - 1;
-                len += (uint32_t)g * 4u + __shfl_sync(FULL_MASK, nbytes, g);
-                break;
-            }
-            if (len < 4u) {                       // cannot happen for a verified candidate inside the limits;
-                ip = mpos + 1; continue;          // kept as a guard against emitting an invalid match
-            }
-            const uint32_t ll = mpos - anchor;
-            if (nseq == 0) { first_ll = ll; first_hdr = 1u + len_bytes(ll); }
-            o = emit_sequence(out, o, base + anchor, ll, mpos - cpos, len - 4u, lane);
-            ++nseq;
-            ip = mpos + len; anchor = ip;
-            // seed the table with a position near the end of the match (the reference does the same with ip-2)
-            if (lane == 0 && ip - 2u >= b0 + 0u && ip - 2u < limit) {
-                uint32_t pp = ip - 2u;
-                tab[hash4(ld32u(base + pp))] = (uint16_t)(pp - b0);
+            } else ++miss;
+            // ---- 4. insert the positions that stayed outside every match
+            {
+                const uint32_t Cm[4] = {C0, C1, C2, C3};
+                #pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (ok[k] && !((Cm[k] >> lane) & 1u)) tab[h[k]] = (uint16_t)rel[k];
             }
             __syncwarp();
+            T0 += span;
+            if (T0 < ip) T0 = ip;
+        }
+        if (npend) {
+            if (nseq == 0) { first_ll = __shfl_sync(FULL_MASK, pd.ll, 0); first_hdr = 1u + len_bytes(first_ll); }
+            o = emit_batch(out, o, base, npend, pd, lane);
+            nseq += npend; npend = 0;
         }
 
         uint32_t tail = b1 - anchor;
