@@ -10,6 +10,8 @@ constexpr unsigned FULL_MASK = 0xffffffffu;
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+
 // 4 bytes at an arbitrary address, little endian.  Touches only the aligned words that contain them.
 __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
     uintptr_t a = (uintptr_t)p;

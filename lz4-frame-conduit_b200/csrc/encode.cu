@@ -19,7 +19,8 @@ namespace b2 {
 
 constexpr uint32_t HSIZE = 1u << ENC_HLOG;
 
-size_t find_emit_smem_bytes() { return (size_t)ENC_WARPS * HSIZE * sizeof(uint16_t); }
+size_t find_emit_smem_bytes() { return (size_t)ENC_SMEM_WARPS * HSIZE * sizeof(uint16_t); }
+size_t find_emit_gtab_bytes(uint32_t grid) { return (size_t)grid * (ENC_WARPS - ENC_SMEM_WARPS) * HSIZE * sizeof(uint16_t); }
 
 __device__ __forceinline__ uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - ENC_HLOG); }
 
@@ -34,6 +35,26 @@ __device__ __forceinline__ uint32_t put_len_ext(uint8_t* out, uint32_t o, uint32
     for (uint32_t i = lane; i < n255; i += 32) out[o + i] = 255;
     if (lane == 0) out[o + n255] = (uint8_t)(r - n255 * 255u);
     return o + n255 + 1u;
+}
+
+constexpr uint32_t NX_LONG = 254u, NX_NONE = 255u;     // link values: match end unknown yet / no further hit
+
+// First hit (bit set in the 128-bit map H0..H3) at index >= j, or NX_NONE.  a1/a2/a3 = first hit in words 1..3 / 2..3 / 3.
+__device__ __forceinline__ uint32_t first_hit_from(uint32_t j, uint32_t H0, uint32_t H1, uint32_t H2, uint32_t H3,
+                                                   uint32_t a1, uint32_t a2, uint32_t a3) {
+    if (j >= 128u) return NX_NONE;
+    const uint32_t w = j >> 5;
+    const uint32_t m = (w == 0 ? H0 : w == 1 ? H1 : w == 2 ? H2 : H3) & (0xFFFFFFFFu << (j & 31u));
+    if (m) return (w << 5) + (uint32_t)__ffs(m) - 1u;
+    return w == 0 ? a1 : w == 1 ? a2 : w == 2 ? a3 : NX_NONE;
+}
+
+// bits [j0, j1) of a 128-bit map, restricted to the 32-bit word that starts at bit `w0`
+__device__ __forceinline__ uint32_t range_mask(uint32_t j0, uint32_t j1, uint32_t w0) {
+    const uint32_t lo = j0 > w0 ? j0 - w0 : 0u, hi = j1 > w0 ? j1 - w0 : 0u;
+    if (lo >= 32u || hi <= lo) return 0u;
+    const uint32_t below_hi = hi >= 32u ? 0xFFFFFFFFu : ((1u << hi) - 1u);
+    return below_hi & (0xFFFFFFFFu << lo);
 }
 
 constexpr uint32_t ENC_LANE_CAP = 32;     // literal runs up to this many bytes are copied one-lane-per-sequence
@@ -94,11 +115,16 @@ __device__ __forceinline__ uint32_t emit_batch(uint8_t* __restrict__ out, uint32
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(ENC_WARPS * 32, 3)
 find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restrict__ scratch,
-                 SubOut* __restrict__ subs, uint32_t* __restrict__ ticket)
+                 SubOut* __restrict__ subs, uint32_t* __restrict__ ticket, uint16_t* __restrict__ gtab)
 {
     extern __shared__ __align__(16) uint16_t s_tab[];
     const uint32_t lane = lane_id();
-    uint16_t* tab = s_tab + (threadIdx.x >> 5) * HSIZE;
+    // half of the CTA's warps keep their hash table in shared memory, the other half in a global table that
+    // lives in L1/L2: twice the warps per SM for the same shared memory, and the extra look-up latency is
+    // small next to the candidate fetches every step already waits for
+    const uint32_t wid = threadIdx.x >> 5;
+    uint16_t* tab = wid < (uint32_t)ENC_SMEM_WARPS ? s_tab + wid * HSIZE
+                  : gtab + ((size_t)blockIdx.x * (ENC_WARPS - ENC_SMEM_WARPS) + (wid - ENC_SMEM_WARPS)) * HSIZE;
 
     for (;;) {
         uint32_t s = 0;
@@ -134,6 +160,8 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 
         while (T0 < limit) {
             const uint32_t sl = miss < 3u ? miss : 3u;                        // probe stride 1, 2, 4, 8
+            const uint32_t span = 128u << sl;
+            if (lane < 2u && T0 + span + 128u * (lane + 1u) <= usize) prefetch_l1(base + T0 + span + 128u * lane);   // next step's input
             // ---- 1. probe
             uint32_t v[4], h[4], rel[4]; int32_t c[4]; bool ok[4];
             #pragma unroll
@@ -149,72 +177,127 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 const uint32_t cl = tab[h[k]];
                 int32_t cc = (int32_t)((rel[k] & ~0xFFFFu) | cl);
                 if ((uint32_t)cc >= rel[k]) cc -= 65536;
-                c[k] = cc;
+                c[k] = (ok[k] && cc >= 0 && rel[k] - (uint32_t)cc < 65536u) ? cc : -1;
             }
-            // ---- 2. verify
-            uint32_t H[4];
+            // ---- 2. verify: one round trip fetches 4 bytes before and 12 bytes after every candidate, so that
+            // most matches are fully measured here (forward length up to 12, backward up to 4) and the serial
+            // selection below rarely has to touch memory
+            uint32_t H[4], pk[4];
             #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 bool hit = false;
-                if (ok[k] && c[k] >= 0 && rel[k] - (uint32_t)c[k] < 65536u) hit = (ld32u(base + b0 + c[k]) == v[k]);
+                pk[k] = 0;
+                if (c[k] >= 0) {
+                    const uint8_t* cp = base + b0 + c[k];
+                    const uint8_t* pp = base + b0 + rel[k];
+                    const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
+                    const uint32_t* pw = (const uint32_t*)((uintptr_t)pp & ~(uintptr_t)3);
+                    const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
+                    const bool bk_ok = c[k] >= 4;                             // 4 bytes in front of the candidate are inside the sub-block
+                    const uint32_t c0 = cw[0], c1 = cw[1], c2 = cw[2], c3 = csh ? cw[3] : 0u, cm = bk_ok ? cw[-1] : 0u;
+                    const uint32_t p0 = pw[0], p1 = pw[1], p2 = pw[2], p3 = psh ? pw[3] : 0u, pm = bk_ok ? pw[-1] : 0u;
+                    const uint32_t x1 = __funnelshift_r(c0, c1, csh) ^ __funnelshift_r(p0, p1, psh);
+                    if (x1 == 0u) {
+                        hit = true;
+                        const uint32_t x2 = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, psh);
+                        const uint32_t x3 = __funnelshift_r(c2, c3, csh) ^ __funnelshift_r(p2, p3, psh);
+                        uint32_t fl = 4u + (x2 ? ((uint32_t)(__ffs(x2) - 1) >> 3) : 4u + (x3 ? ((uint32_t)(__ffs(x3) - 1) >> 3) : 4u));
+                        const uint32_t room = matchlimit - (b0 + rel[k]);     // >= 7 for every probed position
+                        if (fl > room) fl = room;
+                        uint32_t bk = 0;
+                        if (bk_ok) {
+                            const uint32_t x0 = __funnelshift_r(cm, c0, csh) ^ __funnelshift_r(pm, p0, psh);
+                            bk = x0 ? ((uint32_t)__clz(x0) >> 3) : 4u;
+                        }
+                        pk[k] = (uint32_t)c[k] | (fl << 22) | (bk << 26);
+                    }
+                }
                 H[k] = __ballot_sync(FULL_MASK, hit);
             }
-            const uint32_t span = 128u << sl;
-            uint32_t C0 = 0, C1 = 0, C2 = 0, C3 = 0;                          // sample indices swallowed by a match
+            uint32_t C0 = 0, C1 = 0, C2 = 0, C3 = 0;                          // samples swallowed by a match (uniform)
             if ((H[0] | H[1] | H[2] | H[3]) != 0u) {
                 miss = 0;
-                // ---- 3. select
-                uint32_t q = 0;                                               // next sample index to consider
-                while (q < 128u) {
-                    uint32_t kq = q >> 5, m;
-                    m = (kq == 0 ? H[0] : kq == 1 ? H[1] : kq == 2 ? H[2] : H[3]) & (0xFFFFFFFFu << (q & 31u));
-                    while (m == 0u && ++kq < 4u) m = (kq == 1 ? H[1] : kq == 2 ? H[2] : H[3]);
-                    if (m == 0u) break;
-                    const uint32_t ln = (uint32_t)__ffs(m) - 1u, idx = kq * 32u + ln;
-                    const int32_t csel = kq == 0 ? c[0] : kq == 1 ? c[1] : kq == 2 ? c[2] : c[3];
-                    uint32_t mpos = T0 + (idx << sl);
-                    uint32_t cpos = b0 + (uint32_t)__shfl_sync(FULL_MASK, csel, ln);
-                    // backward extension (up to 32 bytes), bounded by the pending literals and the sub-block start
-                    {
-                        const uint32_t mb = mpos - anchor, cb = cpos - b0;
-                        const uint32_t maxback = mb < cb ? mb : cb;
-                        const bool eq = lane < maxback && base[mpos - 1 - lane] == base[cpos - 1 - lane];
-                        const uint32_t ne = __ballot_sync(FULL_MASK, !eq);
-                        const uint32_t back = ne ? (uint32_t)(__ffs(ne) - 1) : 32u;
-                        mpos -= back; cpos -= back;
+                // ---- 3a. link: every hit computes where the greedy parse goes next if it is taken — the first hit
+                // at or after its end (lane-parallel; ends of 12+-byte matches are not known yet -> NX_LONG)
+                const uint32_t a3 = H[3] ? 95u + (uint32_t)__ffs(H[3]) : NX_NONE;          // first hit in word 3
+                const uint32_t a2 = H[2] ? 63u + (uint32_t)__ffs(H[2]) : a3;               // ... in words 2..3
+                const uint32_t a1 = H[1] ? 31u + (uint32_t)__ffs(H[1]) : a2;               // ... in words 1..3
+                uint32_t NX = 0;
+                #pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    uint32_t nx = NX_NONE;
+                    if (pk[k]) {
+                        const uint32_t fl = (pk[k] >> 22) & 15u;
+                        if (fl >= 12u) nx = NX_LONG;
+                        else nx = first_hit_from(32u * k + lane + ((fl + (1u << sl) - 1u) >> sl), H[0], H[1], H[2], H[3], a1, a2, a3);
                     }
-                    // forward extension: every lane compares 4 bytes; bytes at and after matchlimit never count
-                    uint32_t len = 0;
+                    NX |= nx << (8 * k);
+                }
+                // ---- 3b. select: follow the links from the first hit; lane `npend` takes the next match
+                uint32_t cur = H[0] ? (uint32_t)__ffs(H[0]) - 1u : a1;
+                while (cur != NX_NONE) {
+                    const uint32_t s0 = npend;
+                    uint32_t my_idx = 0, nx;
                     for (;;) {
-                        const uint32_t qq = mpos + len + lane * 4u;
-                        const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
-                        uint32_t nbytes = 0;
-                        if (avail) {
-                            const uint32_t xx = ld32u(base + qq) ^ ld32u(base + cpos + len + lane * 4u);
-                            nbytes = xx ? (uint32_t)(__ffs(xx) - 1) >> 3 : 4u;
-                            if (nbytes > avail) nbytes = avail;
+                        nx = (__shfl_sync(FULL_MASK, NX, cur & 31u) >> ((cur >> 5) * 8u)) & 255u;
+                        if (lane == npend) my_idx = cur;
+                        ++npend;
+                        if (nx >= NX_LONG || npend == 32u) break;
+                        cur = nx;
+                    }
+                    // ---- 3c. the lanes s0 .. npend-1 turn their match into a sequence
+                    const bool mine = lane >= s0 && lane < npend;
+                    const uint32_t own = my_idx & 31u, kk = my_idx >> 5;
+                    const uint32_t g0 = __shfl_sync(FULL_MASK, pk[0], own), g1 = __shfl_sync(FULL_MASK, pk[1], own);
+                    const uint32_t g2 = __shfl_sync(FULL_MASK, pk[2], own), g3 = __shfl_sync(FULL_MASK, pk[3], own);
+                    const uint32_t pkv = kk == 0 ? g0 : kk == 1 ? g1 : kk == 2 ? g2 : g3;
+                    const uint32_t pos = T0 + (my_idx << sl);
+                    uint32_t fl = (pkv >> 22) & 15u;
+                    uint32_t mend = pos + fl;
+                    if (nx == NX_LONG) {
+                        // the last match taken is 12+ bytes: measure it with the whole warp (4 bytes per lane per round;
+                        // bytes at and after matchlimit never count)
+                        const uint32_t lp = __shfl_sync(FULL_MASK, pos, npend - 1u);
+                        const uint32_t lc = b0 + (__shfl_sync(FULL_MASK, pkv, npend - 1u) & 0x3FFFFFu);
+                        uint32_t len = 12u;
+                        for (;;) {
+                            const uint32_t qq = lp + len + lane * 4u;
+                            const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
+                            uint32_t nbytes = 0;
+                            if (avail) {
+                                const uint32_t xx = ld32u(base + qq) ^ ld32u(base + lc + len + lane * 4u);
+                                nbytes = xx ? (uint32_t)(__ffs(xx) - 1) >> 3 : 4u;
+                                if (nbytes > avail) nbytes = avail;
+                            }
+                            const uint32_t part = __ballot_sync(FULL_MASK, nbytes != 4u);
+                            if (part == 0) { len += 128u; continue; }
+                            const int g = __ffs(part) - 1;
+                            len += (uint32_t)g * 4u + __shfl_sync(FULL_MASK, nbytes, g);
+                            break;
                         }
-                        const uint32_t part = __ballot_sync(FULL_MASK, nbytes != 4u);
-                        if (part == 0) { len += 128u; continue; }
-                        const int g = __ffs(part) - 1;
-                        len += (uint32_t)g * 4u + __shfl_sync(FULL_MASK, nbytes, g);
-                        break;
+                        if (lane == npend - 1u) { fl = len; mend = pos + len; }
                     }
-                    if (len < 4u) { q = idx + 1u; continue; }                 // guard: never emit an invalid match
-                    if (lane == npend) { pd.anchor = anchor; pd.ll = mpos - anchor; pd.off = mpos - cpos; pd.mlc = len - 4u; }
-                    ++npend;
-                    const uint32_t mend = mpos + len;
-                    anchor = ip = mend;
-                    // sample indices strictly inside the match: ((mpos - T0) >> sl) + 1 .. first index at or after mend
-                    const uint32_t j0 = mpos >= T0 ? ((mpos - T0) >> sl) + 1u : 0u;
-                    uint32_t j1 = (mend - T0 + (1u << sl) - 1u) >> sl; if (j1 > 128u) j1 = 128u;
-                    if (j1 > j0) {
-                        #define B2_RANGE(lo, hi, w) { uint32_t a_ = lo > 32u * w ? lo - 32u * w : 0u, b_ = hi > 32u * w ? hi - 32u * w : 0u; \
-                            if (a_ < 32u && b_ > a_) { uint32_t mk = 0xFFFFFFFFu << a_; if (b_ < 32u) mk &= ~(0xFFFFFFFFu << b_); C##w |= mk; } }
-                        B2_RANGE(j0, j1, 0) B2_RANGE(j0, j1, 1) B2_RANGE(j0, j1, 2) B2_RANGE(j0, j1, 3)
-                        #undef B2_RANGE
+                    uint32_t prev_end = __shfl_up_sync(FULL_MASK, mend, 1);
+                    if (lane == s0) prev_end = anchor;
+                    uint32_t j0 = 0, j1 = 0;
+                    if (mine) {
+                        uint32_t back = pkv >> 26;
+                        if (back > pos - prev_end) back = pos - prev_end;
+                        const uint32_t mpos = pos - back;
+                        pd.anchor = prev_end; pd.ll = mpos - prev_end; pd.off = pos - (b0 + (pkv & 0x3FFFFFu)); pd.mlc = fl + back - 4u;
+                        // sample indices strictly inside the match: ((mpos - T0) >> sl) + 1 .. first index at or after mend
+                        j0 = mpos >= T0 ? ((mpos - T0) >> sl) + 1u : 0u;
+                        j1 = (mend - T0 + (1u << sl) - 1u) >> sl;
                     }
-                    q = j1;
+                    C0 |= __reduce_or_sync(FULL_MASK, range_mask(j0, j1, 0u));
+                    C1 |= __reduce_or_sync(FULL_MASK, range_mask(j0, j1, 32u));
+                    C2 |= __reduce_or_sync(FULL_MASK, range_mask(j0, j1, 64u));
+                    C3 |= __reduce_or_sync(FULL_MASK, range_mask(j0, j1, 96u));
+                    anchor = ip = __shfl_sync(FULL_MASK, mend, npend - 1u);
+                    if (nx == NX_LONG) {
+                        const uint32_t jl = __shfl_sync(FULL_MASK, j1, npend - 1u);
+                        cur = first_hit_from(jl, H[0], H[1], H[2], H[3], a1, a2, a3);
+                    } else cur = nx;                                          // NX_NONE, or the next hit when the batch filled up
                     if (npend == 32u) {
                         if (nseq == 0) { first_ll = __shfl_sync(FULL_MASK, pd.ll, 0); first_hdr = 1u + len_bytes(first_ll); }
                         o = emit_batch(out, o, base, npend, pd, lane);

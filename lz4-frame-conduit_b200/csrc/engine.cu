@@ -62,7 +62,7 @@ struct b2lz4_ctx {
     cudaEvent_t ev_in = nullptr, ev_sum = nullptr;
     Small* d_small = nullptr;
     Small* h_small = nullptr;                     // pinned
-    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out;
+    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out, enc_tabs;
     b2lz4_stats stats{};
     char cuda_err[256] = {0};
     int sm_count = 148;
@@ -199,7 +199,7 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->st) cudaStreamSynchronize(ctx->st);
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
-                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out }) b->release();
+                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& v : ctx->ev) if (v) cudaEventDestroy(v);
@@ -277,8 +277,9 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
     if (P.n_subs) {
         uint32_t grid = std::min<uint32_t>((P.n_subs + ENC_WARPS - 1) / ENC_WARPS, (uint32_t)ctx->sm_count * 3u);
+        CU(ctx->enc_tabs.ensure(find_emit_gtab_bytes(grid)));
         find_emit_kernel<<<grid, ENC_WARPS * 32, find_emit_smem_bytes(), ctx->st>>>(
-            d_src, P, (uint8_t*)ctx->scratch.p, (SubOut*)ctx->subs.p, &ds->ticket_enc);
+            d_src, P, (uint8_t*)ctx->scratch.p, (SubOut*)ctx->subs.p, &ds->ticket_enc, (uint16_t*)ctx->enc_tabs.p);
         ++launches;
     }
     CU(cudaEventRecord(ctx->ev[1], ctx->st));

@@ -7,7 +7,8 @@
 namespace b2 {
 
 constexpr int DEC_WARPS = 4;          // warps per CTA in the sequence decoder
-constexpr int ENC_WARPS = 4;          // warps per CTA in the match finder (one hash table each)
+constexpr int ENC_WARPS = 8;          // warps per CTA in the match finder (one hash table each)
+constexpr int ENC_SMEM_WARPS = 4;     // ... of which this many keep their table in shared memory; the others use a global (L1/L2) table
 constexpr int ENC_HLOG  = 13;         // 8192-entry u16 hash table per warp (16 KB)
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u };
 
@@ -24,7 +25,8 @@ __global__ void verify_block_checksums_kernel(const uint8_t* src, const FrameInd
                                               const BlockRef* blocks, uint32_t* first_bad);
 
 // ---- encode
-__global__ void find_emit_kernel(const uint8_t* src, EncParams P, uint8_t* scratch, SubOut* subs, uint32_t* ticket);
+__global__ void find_emit_kernel(const uint8_t* src, EncParams P, uint8_t* scratch, SubOut* subs, uint32_t* ticket, uint16_t* gtab);
+size_t find_emit_gtab_bytes(uint32_t grid);
 __global__ void layout_kernel(EncParams P, const SubOut* subs, SubPlace* places, BlockPlace* bplaces,
                               uint8_t* dst, uint64_t dst_cap, EncodeResult* res, uint32_t* ticket);
 __global__ void gather_kernel(const uint8_t* src, EncParams P, const uint8_t* scratch, const SubOut* subs,
