@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200lz4.so")
+LIB_PATH = os.environ.get("B2LZ4_LIB") or os.path.join(_HERE, "libb200lz4.so")   # B2LZ4_LIB: tuning builds (tools/variants.sh)
 
 
 class Prefs(C.Structure):

@@ -276,7 +276,7 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     }
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
     if (P.n_subs) {
-        uint32_t grid = std::min<uint32_t>((P.n_subs + ENC_WARPS - 1) / ENC_WARPS, (uint32_t)ctx->sm_count * 3u);
+        uint32_t grid = std::min<uint32_t>((P.n_subs + ENC_WARPS - 1) / ENC_WARPS, (uint32_t)ctx->sm_count * (uint32_t)ENC_CTAS_PER_SM);
         CU(ctx->enc_tabs.ensure(find_emit_gtab_bytes(grid)));
         find_emit_kernel<<<grid, ENC_WARPS * 32, find_emit_smem_bytes(), ctx->st>>>(
             d_src, P, (uint8_t*)ctx->scratch.p, (SubOut*)ctx->subs.p, &ds->ticket_enc, (uint16_t*)ctx->enc_tabs.p);
