@@ -91,6 +91,22 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* ds
 void*  b2lz4_pinned_alloc(size_t n);
 void   b2lz4_pinned_free(void* p);
 
+/* ---- streaming pieces: a conduit that cuts the stream into batches of whole blocks itself calls these
+ * (they are what the LZ4F_* layer in lz4frame.h is built on).  Replaces the LZ4F_compressUpdate /
+ * LZ4F_compressEnd / LZ4F_decompress inner loops (lz4frame.c:823-925, 984-1018, 1371-1840) with one call
+ * per batch.  Prefs of the context decide block size / checksums. */
+#define B2LZ4_STREAM_FIRST 1u   /* first batch of a frame: resets the running content checksum and the decode history */
+/* n bytes -> [u32 size|stored][data][block checksum]... ; n must be a multiple of the block size except in the last batch */
+size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, unsigned flags);
+/* EndMark + content checksum (when enabled) of everything compressed since B2LZ4_STREAM_FIRST: 4 or 8 bytes */
+size_t b2lz4_frame_end(b2lz4_ctx* ctx, void* dst, size_t cap);
+/* n bytes of WHOLE blocks of a frame described by `info` (no frame header, no EndMark) -> decoded bytes.
+ * Linked-block frames keep their 64 KB history on the device between calls. */
+size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info, const void* src, size_t n,
+                                    void* dst, size_t cap, unsigned flags);
+/* XXH32 of everything compressed / decoded since B2LZ4_STREAM_FIRST (content checksum, xxhash.c:529-554) */
+size_t b2lz4_content_checksum(b2lz4_ctx* ctx, uint32_t* out);
+
 /* ---- XXH32 of a device / host buffer, seed 0 (replaces XXH32, xxhash.c:392-416) */
 size_t b2lz4_xxh32_device(b2lz4_ctx* ctx, const void* d_src, size_t n, uint32_t* out);
 size_t b2lz4_xxh32_host(b2lz4_ctx* ctx, const void* src, size_t n, uint32_t* out);

@@ -52,6 +52,10 @@ SYMBOLS = {
     "b2lz4_decompress_host": (_sz, [_vp, _vp, _sz, _vp, _sz, _szp]),
     "b2lz4_pinned_alloc": (_vp, [_sz]),
     "b2lz4_pinned_free": (None, [_vp]),
+    "b2lz4_compress_blocks_host": (_sz, [_vp, _vp, _sz, _vp, _sz, C.c_uint]),
+    "b2lz4_frame_end": (_sz, [_vp, _vp, _sz]),
+    "b2lz4_decompress_blocks_host": (_sz, [_vp, C.POINTER(FrameInfo), _vp, _sz, _vp, _sz, C.c_uint]),
+    "b2lz4_content_checksum": (_sz, [_vp, _u32p]),
     "b2lz4_xxh32_device": (_sz, [_vp, _vp, _sz, _u32p]),
     "b2lz4_xxh32_host": (_sz, [_vp, _vp, _sz, _u32p]),
     "b2lz4_last_stats": (_sz, [_vp, C.POINTER(Stats)]),

@@ -408,8 +408,10 @@ __global__ void __launch_bounds__(DEC_WARPS * 32)
 decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint64_t dst_cap,
                      const FrameIndex* __restrict__ fi, const BlockRef* __restrict__ blocks,
                      const Piece* __restrict__ pieces, const Chain* __restrict__ chains,
-                     PieceOut* __restrict__ outs, uint32_t* __restrict__ ticket)
+                     PieceOut* __restrict__ outs, uint32_t* __restrict__ ticket, uint32_t hist)
 {
+    // hist = bytes of earlier output of the same linked-block frame that lie directly in front of dst
+    // (streaming decode in batches: lz4frame.c:1286-1349 keeps the same 64 KB)
     if (fi->err != OK) return;
     const uint32_t lane = lane_id();
     const uint32_t n_chains = fi->n_chains;
@@ -452,7 +454,7 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
                 if (cu.opiece_end > ocap && !(pc.flags & PIECE_EXACT)) cu.opiece_end = ocap;
                 // window start: independent blocks/sub-blocks may only reference their own output;
                 // linked blocks reach up to 64 KB into the earlier output of the chain (lz4frame.c:1286-1349)
-                if (linked) { uint64_t h = blk_out - chain_start; cu.reach = h > 0x40000000ull ? 0x40000000u : (uint32_t)h; }
+                if (linked) { uint64_t h = blk_out - chain_start + hist; cu.reach = h > 0x40000000ull ? 0x40000000u : (uint32_t)h; }
                 else cu.reach = 0u - op_rel;
                 uint32_t e = decode_piece(cu, (pc.flags & PIECE_ENDS_BLOCK) != 0);
                 const uint32_t produced = cu.op - op_rel;

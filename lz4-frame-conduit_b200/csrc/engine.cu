@@ -62,7 +62,8 @@ struct b2lz4_ctx {
     cudaEvent_t ev_in = nullptr, ev_sum = nullptr;
     Small* d_small = nullptr;
     Small* h_small = nullptr;                     // pinned
-    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out, enc_tabs;
+    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out, enc_tabs, ring;
+    size_t ring_pos = 0; uint32_t ring_hist = 0;     // streaming linked-block decode: next output offset / valid history bytes
     b2lz4_stats stats{};
     char cuda_err[256] = {0};
     int sm_count = 148;
@@ -199,7 +200,7 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->st) cudaStreamSynchronize(ctx->st);
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
-                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs }) b->release();
+                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& v : ctx->ev) if (v) cudaEventDestroy(v);
@@ -235,9 +236,11 @@ void b2lz4_pinned_free(void* p) { if (p) cudaFreeHost(p); }
 // -------------------------------------------------------------------------------------- compress
 // Launch sequence on ctx->st: find_emit -> layout -> gather -> [block checksums] ; the content checksum
 // runs on ctx->st2 over the input, concurrently, and its digest is stored once layout knows the offset.
+enum : unsigned { CL_WHOLE_FRAME = 1u, CL_SUM_RESET = 2u, CL_SUM_UPDATE = 4u };
 static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, uint8_t* d_dst, size_t cap,
-                              bool whole_frame)
+                              unsigned flags)
 {
+    const bool whole_frame = (flags & CL_WHOLE_FRAME) != 0;
     const b2lz4_prefs& pr = ctx->prefs;
     EncParams P{};
     P.n = n;
@@ -265,14 +268,13 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
 
     Small* ds = ctx->d_small;
     uint32_t launches = 0;
-    const bool sum = P.content_checksum != 0;
+    const bool sum = P.desc.content_checksum != 0 && (flags & (CL_SUM_RESET | CL_SUM_UPDATE)) != 0;
     if (sum) {                                   // serial XXH32 of the input on the second stream
         CU(cudaEventRecord(ctx->ev_in, ctx->st));
         CU(cudaStreamWaitEvent(ctx->st2, ctx->ev_in, 0));
-        xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh);
-        xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>(d_src, n, nullptr, nullptr, &ds->xxh);
+        if (flags & CL_SUM_RESET) { xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh); ++launches; }
+        if (flags & CL_SUM_UPDATE) { xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>(d_src, n, nullptr, nullptr, &ds->xxh); ++launches; }
         CU(cudaEventRecord(ctx->ev_sum, ctx->st2));
-        launches += 2;
     }
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
     if (P.n_subs) {
@@ -300,8 +302,10 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     }
     if (sum) {
         CU(cudaStreamWaitEvent(ctx->st, ctx->ev_sum, 0));
-        xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, d_dst, &ds->eres.content_checksum_off);
-        ++launches;
+        if (whole_frame) {
+            xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, d_dst, &ds->eres.content_checksum_off);
+            ++launches;
+        }
     }
     CU(cudaEventRecord(ctx->ev[2], ctx->st));
     CU(cudaMemcpyAsync(&ctx->h_small->eres, &ds->eres, sizeof(EncodeResult), cudaMemcpyDeviceToHost, ctx->st));
@@ -328,14 +332,14 @@ size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* 
     if (!ctx || (!d_src && n) || !d_dst) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
     ctx->stats = b2lz4_stats{};
-    r = compress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, true);
+    r = compress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, CL_WHOLE_FRAME | CL_SUM_RESET | CL_SUM_UPDATE);
     if (r) return r;
     return compress_finish(ctx, n);
 }
 
 // -------------------------------------------------------------------------------------- decompress
 static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, uint8_t* d_dst, size_t cap,
-                                uint32_t mode, uint32_t cap_tables)
+                                uint32_t mode, uint32_t cap_tables, uint32_t hist)
 {
     CU(ctx->blocks.ensure((size_t)cap_tables * sizeof(BlockRef)));
     CU(ctx->pieces.ensure((size_t)cap_tables * sizeof(Piece)));
@@ -352,16 +356,19 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
     decode_chains_kernel<<<ctx->sm_count * (64 / DEC_WARPS), DEC_WARPS * 32, 0, ctx->st>>>(
         d_src, d_dst, cap, &ds->fi, (const BlockRef*)ctx->blocks.p, (const Piece*)ctx->pieces.p,
-        (const Chain*)ctx->chains.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec);
+        (const Chain*)ctx->chains.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec, hist);
     CU(cudaEventRecord(ctx->ev[2], ctx->st));
     decode_finalize_kernel<<<1, 256, 0, ctx->st>>>(&ds->fi, (const Piece*)ctx->pieces.p, (const PieceOut*)ctx->outs.p,
                                                    &ds->crc_bad, &ds->dres, &ds->ticket_dec);
     // content checksum over the output (lz4frame.c:1676-1677, 1734-1745); the kernels return at once
     // when the frame carries none
-    xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
-    xxh32_stream_kernel<<<1, 256, 0, ctx->st>>>(d_dst, 0, &ds->dres.total_out, &ds->fi.desc.content_checksum, &ds->xxh);
-    content_check_kernel<<<1, 32, 0, ctx->st>>>(&ds->fi, &ds->xxh, &ds->dres);
-    launches += 7;
+    if (!(mode & SCAN_BATCH)) {                   // a batch of a streamed frame keeps its running checksum (caller updates it)
+        xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
+        xxh32_stream_kernel<<<1, 256, 0, ctx->st>>>(d_dst, 0, &ds->dres.total_out, &ds->fi.desc.content_checksum, &ds->xxh);
+        content_check_kernel<<<1, 32, 0, ctx->st>>>(&ds->fi, &ds->xxh, &ds->dres);
+        launches += 3;
+    }
+    launches += 4;
     CU(cudaEventRecord(ctx->ev[3], ctx->st));
     CU(cudaMemcpyAsync(&ctx->h_small->fi, &ds->fi, sizeof(FrameIndex) + sizeof(DecodeResult), cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaGetLastError());
@@ -371,7 +378,13 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
 
 static_assert(offsetof(Small, dres) == sizeof(FrameIndex), "fi and dres must be contiguous for the single copy");
 
+static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed,
+                                     uint32_t hist, uint32_t mode0 = 0u);
 size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed) {
+    return decompress_device_impl(ctx, d_src, n, d_dst, cap, consumed, 0u);
+}
+static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed,
+                                     uint32_t hist, uint32_t mode0) {
     if (consumed) *consumed = 0;
     if (!ctx || !d_src || (!d_dst && cap)) return err_code(E_GENERIC);
     if (n < (size_t)HEADER_MIN) return err_code(E_frameHeader_incomplete);
@@ -380,10 +393,10 @@ size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void
     static uint8_t* dummy = nullptr;
     uint8_t* dst = (uint8_t*)d_dst;
     if (!dst) { if (!dummy) CU(cudaMalloc(&dummy, 256)); dst = dummy; }
-    uint32_t mode = ctx->prefs.use_index ? SCAN_USE_INDEX : 0u;
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u);
     uint32_t cap_tables = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, std::max<uint64_t>(4096, (n >> 12) + (cap >> 16) + 64));
     for (int attempt = 0; attempt < 4; ++attempt) {
-        r = decompress_launch(ctx, (const uint8_t*)d_src, n, dst, cap, mode, cap_tables);
+        r = decompress_launch(ctx, (const uint8_t*)d_src, n, dst, cap, mode, cap_tables, hist);
         if (r) return r;
         CU(cudaStreamSynchronize(ctx->st));
         const FrameIndex& fi = ctx->h_small->fi;
@@ -424,7 +437,7 @@ size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst,
     CU(cudaEventRecord(ctx->ev[4], ctx->st));
     if (n) CU(cudaMemcpyAsync(ctx->stage_in.p, src, n, cudaMemcpyHostToDevice, ctx->st));
     CU(cudaEventRecord(ctx->ev[5], ctx->st));
-    r = compress_launch(ctx, (const uint8_t*)ctx->stage_in.p, n, (uint8_t*)ctx->stage_out.p, std::min(bound, cap), true);
+    r = compress_launch(ctx, (const uint8_t*)ctx->stage_in.p, n, (uint8_t*)ctx->stage_out.p, std::min(bound, cap), CL_WHOLE_FRAME | CL_SUM_RESET | CL_SUM_UPDATE);
     if (r) return r;
     r = compress_finish(ctx, n);
     if (b2lz4_is_error(r)) return r;
@@ -455,6 +468,129 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* ds
     CU(cudaStreamSynchronize(ctx->st));
     cudaEventElapsedTime(&ctx->stats.ms_h2d, e0, e1);
     cudaEventElapsedTime(&ctx->stats.ms_d2h, e2, e3);
+    return r;
+}
+
+// -------------------------------------------------------------------------------------- streaming (batches of blocks)
+size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, unsigned flags) {
+    if (!ctx || (!src && n) || !dst) return err_code(E_GENERIC);
+    size_t r = set_device(ctx); if (r) return r;
+    ctx->stats = b2lz4_stats{};
+    if (n == 0) {                                                   // nothing to emit, but the checksum may have to restart
+        if ((flags & B2LZ4_STREAM_FIRST) && ctx->prefs.content_checksum) {
+            xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ctx->d_small->xxh);
+            CU(cudaStreamSynchronize(ctx->st));
+        }
+        return 0;
+    }
+    size_t bound = b2lz4_compress_bound(n, &ctx->prefs);
+    CU(ctx->stage_in.ensure(n + 16));
+    CU(ctx->stage_out.ensure(bound + 16));
+    CU(cudaMemcpyAsync(ctx->stage_in.p, src, n, cudaMemcpyHostToDevice, ctx->st));
+    r = compress_launch(ctx, (const uint8_t*)ctx->stage_in.p, n, (uint8_t*)ctx->stage_out.p, std::min(bound, cap),
+                        CL_SUM_UPDATE | ((flags & B2LZ4_STREAM_FIRST) ? CL_SUM_RESET : 0u));
+    if (r) return r;
+    r = compress_finish(ctx, n);
+    if (b2lz4_is_error(r)) return r;
+    CU(cudaMemcpyAsync(dst, ctx->stage_out.p, r, cudaMemcpyDeviceToHost, ctx->st));
+    CU(cudaStreamSynchronize(ctx->st));
+    return r;
+}
+
+size_t b2lz4_content_checksum(b2lz4_ctx* ctx, uint32_t* out) {
+    if (!ctx || !out) return err_code(E_GENERIC);
+    size_t r = set_device(ctx); if (r) return r;
+    Small* ds = ctx->d_small;
+    CU(cudaStreamSynchronize(ctx->st2));
+    xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, nullptr, nullptr);
+    CU(cudaMemcpyAsync(&ctx->h_small->hash_out, &ds->hash_out, 4, cudaMemcpyDeviceToHost, ctx->st));
+    CU(cudaStreamSynchronize(ctx->st));
+    CU(cudaGetLastError());
+    *out = ctx->h_small->hash_out;
+    return 0;
+}
+
+size_t b2lz4_frame_end(b2lz4_ctx* ctx, void* dst, size_t cap) {
+    if (!ctx || !dst) return err_code(E_GENERIC);
+    const size_t need = 4u + (ctx->prefs.content_checksum ? 4u : 0u);
+    if (cap < need) return err_code(E_dstMaxSize_tooSmall);
+    uint8_t* d = (uint8_t*)dst;
+    st_le32(d, 0u);                                                 // EndMark (lz4frame.c:998-1000)
+    if (ctx->prefs.content_checksum) {
+        uint32_t h = 0;
+        size_t r = b2lz4_content_checksum(ctx, &h); if (r) return r;
+        st_le32(d + 4, h);
+    }
+    return need;
+}
+
+// keeps `hist` bytes of earlier output directly in front of the place the next batch decodes to
+static size_t ring_reserve(b2lz4_ctx* ctx, size_t cap) {
+    const size_t H = 65536;
+    const size_t want = 2 * H + 2 * cap + 256;
+    if (ctx->ring.cap < want) {                                     // grow, carrying the history over
+        DevBuf nb;
+        CU(nb.ensure(want));
+        if (ctx->ring_hist) CU(cudaMemcpyAsync((uint8_t*)nb.p + H - ctx->ring_hist, (uint8_t*)ctx->ring.p + ctx->ring_pos - ctx->ring_hist,
+                                               ctx->ring_hist, cudaMemcpyDeviceToDevice, ctx->st));
+        CU(cudaStreamSynchronize(ctx->st));
+        ctx->ring.release(); ctx->ring = nb; ctx->ring_pos = H;
+    } else if (ctx->ring_pos + cap + 16 > ctx->ring.cap) {          // wrap: history moves to the front (never overlaps: ring_pos >= 2H here)
+        if (ctx->ring_hist) CU(cudaMemcpyAsync((uint8_t*)ctx->ring.p + H - ctx->ring_hist, (uint8_t*)ctx->ring.p + ctx->ring_pos - ctx->ring_hist,
+                                               ctx->ring_hist, cudaMemcpyDeviceToDevice, ctx->st));
+        ctx->ring_pos = H;
+    }
+    return 0;
+}
+
+size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info, const void* src, size_t n,
+                                    void* dst, size_t cap, unsigned flags) {
+    if (!ctx || !info || (!src && n) || (!dst && cap)) return err_code(E_GENERIC);
+    if (info->block_size_id < 4 || info->block_size_id > 7) return err_code(E_maxBlockSize_invalid);
+    size_t r = set_device(ctx); if (r) return r;
+    Small* ds = ctx->d_small;
+    if (flags & B2LZ4_STREAM_FIRST) {
+        ctx->ring_pos = 65536; ctx->ring_hist = 0;
+        if (info->content_checksum) xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
+    }
+    if (n == 0) { CU(cudaStreamSynchronize(ctx->st)); return 0; }
+    // a frame of its own around the batch: header without optional fields, the blocks, an EndMark
+    FrameDesc d{};
+    d.block_size_id = info->block_size_id; d.block_independent = info->block_independent ? 1u : 0u;
+    d.block_checksum = info->block_checksum ? 1u : 0u;
+    uint8_t hdr[HEADER_MAX];
+    const uint32_t hs = header_write(hdr, d);
+    const uint32_t zero = 0;
+    CU(ctx->stage_in.ensure(hs + n + 4 + 16));
+    uint8_t* din = (uint8_t*)ctx->stage_in.p;
+    CU(cudaMemcpyAsync(din, hdr, hs, cudaMemcpyHostToDevice, ctx->st));
+    CU(cudaMemcpyAsync(din + hs, src, n, cudaMemcpyHostToDevice, ctx->st));
+    CU(cudaMemcpyAsync(din + hs + n, &zero, 4, cudaMemcpyHostToDevice, ctx->st));
+    uint8_t* dout;
+    uint32_t hist = 0;
+    const bool linked = !info->block_independent;
+    if (linked) {
+        r = ring_reserve(ctx, cap); if (r) return r;
+        dout = (uint8_t*)ctx->ring.p + ctx->ring_pos; hist = ctx->ring_hist;
+    } else {
+        CU(ctx->stage_out.ensure(cap + 16));
+        dout = (uint8_t*)ctx->stage_out.p;
+    }
+    const uint32_t keep_index = ctx->prefs.use_index;
+    ctx->prefs.use_index = 0;                                       // a batch never carries an index frame
+    size_t consumed = 0;
+    r = decompress_device_impl(ctx, din, hs + n + 4, dout, cap, &consumed, hist, SCAN_BATCH);
+    ctx->prefs.use_index = keep_index;
+    if (b2lz4_is_error(r)) return r;
+    if (consumed != hs + n + 4) return err_code(E_decompressionFailed);   // an EndMark inside the batch: not whole blocks
+    if (info->content_checksum && r) xxh32_stream_kernel<<<1, 256, 0, ctx->st>>>(dout, r, nullptr, nullptr, &ds->xxh);
+    if (r) CU(cudaMemcpyAsync(dst, dout, r, cudaMemcpyDeviceToHost, ctx->st));
+    CU(cudaStreamSynchronize(ctx->st));
+    CU(cudaGetLastError());
+    if (linked) {
+        ctx->ring_pos += r;
+        ctx->ring_hist = (uint32_t)std::min<size_t>(65536, (size_t)ctx->ring_hist + r);
+    }
     return r;
 }
 

@@ -20,7 +20,7 @@ constexpr int ENC_WARPS = B2_ENC_WARPS;          // warps per CTA in the match f
 constexpr int ENC_SMEM_WARPS = B2_ENC_SMEM_WARPS;     // ... of which this many keep their table in shared memory; the others use a global (L1/L2) table
 constexpr int ENC_CTAS_PER_SM = B2_ENC_CTAS;   // resident CTAs per SM the kernel is built for
 constexpr int ENC_HLOG  = 13;         // 8192-entry u16 hash table per warp (16 KB)
-enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u };
+enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u };
 
 // ---- decode
 __global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_cap, uint32_t mode,
@@ -28,7 +28,7 @@ __global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_c
                                   Piece* pieces, uint32_t cap_pieces, Chain* chains);
 __global__ void decode_chains_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap,
                                      const FrameIndex* fi, const BlockRef* blocks, const Piece* pieces,
-                                     const Chain* chains, PieceOut* outs, uint32_t* ticket);
+                                     const Chain* chains, PieceOut* outs, uint32_t* ticket, uint32_t hist);
 __global__ void decode_finalize_kernel(const FrameIndex* fi, const Piece* pieces, const PieceOut* outs,
                                        const uint32_t* block_crc_bad, DecodeResult* res, uint32_t* ticket);
 __global__ void verify_block_checksums_kernel(const uint8_t* src, const FrameIndex* fi,

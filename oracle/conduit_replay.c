@@ -21,9 +21,13 @@
 #include <string.h>
 #include <stdint.h>
 #include "lz4frame.h"
+/* -DREPLAY_AGAINST_B200: the same replay compiled against include/lz4frame.h and linked to libb200lz4.so —
+ * tests/ use it to drive the product's LZ4F_* layer with exactly the calls the Haskell conduit makes. */
+#ifndef REPLAY_AGAINST_B200
 #include "lz4.h"
 #define XXH_STATIC_LINKING_ONLY
 #include "xxhash.h"
+#endif
 
 #define REPLAY_ERR_DST_TOO_SMALL   ((size_t)-100)
 #define REPLAY_ERR_HEADER_SHORT    ((size_t)-101)  /* Conduit.hsc:615-616 "not enough bytes for header" */
@@ -256,6 +260,7 @@ size_t ref_frame_decompress(const void* src_, size_t n, void* dst_, size_t cap, 
     return r;
 }
 
+#ifndef REPLAY_AGAINST_B200
 unsigned ref_xxh32(const void* p, size_t n, unsigned seed) { return XXH32(p, n, seed); }
 
 /* streaming XXH32 over arbitrary splits (content-checksum behaviour, xxhash.c:437-554) */
@@ -267,6 +272,8 @@ unsigned ref_xxh32_stream(const void* p_, size_t n, unsigned seed, size_t piece)
     for (size_t o = 0; o < n; o += piece) XXH32_update(&st, p + o, MINSZ(piece, n - o));
     return XXH32_digest(&st);
 }
+
+#endif
 
 size_t ref_sizeof_frameinfo(void)   { return sizeof(LZ4F_frameInfo_t); }
 size_t ref_sizeof_preferences(void) { return sizeof(LZ4F_preferences_t); }

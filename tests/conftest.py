@@ -13,6 +13,10 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+# the LZ4F_* layer batches this many MiB per GPU call; small here so that modest test inputs span several batches
+os.environ.setdefault("B2LZ4_BATCH_MB", "8")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
@@ -111,6 +115,44 @@ def ref():
     lib.LZ4_decompress_safe.restype = C.c_int
     lib.LZ4_decompress_safe.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
     return lib
+
+
+def _bind_replay(lib):
+    lib.ref_conduit_compress.restype = sz
+    lib.ref_conduit_compress.argtypes = [C.c_char_p, sz, C.c_char_p, sz, sz, sz]
+    lib.ref_conduit_compress_yi.restype = sz
+    lib.ref_conduit_compress_yi.argtypes = [C.c_char_p, sz, C.c_char_p, sz, sz]
+    lib.ref_conduit_decompress.restype = sz
+    lib.ref_conduit_decompress.argtypes = [C.c_char_p, sz, C.c_char_p, sz, sz, C.POINTER(sz)]
+    lib.ref_frame_decompress.restype = sz
+    lib.ref_frame_decompress.argtypes = [C.c_char_p, sz, C.c_char_p, sz, C.POINTER(sz)]
+    lib.ref_frame_compress.restype = sz
+    lib.ref_frame_compress.argtypes = [C.c_char_p, sz, C.c_char_p, sz] + [C.c_int] * 6 + [sz]
+    lib.ref_sizeof_frameinfo.restype = sz
+    lib.ref_sizeof_preferences.restype = sz
+    return lib
+
+
+def build_replay_b200():
+    """tests/_build/libreplay_b200.so: oracle/conduit_replay.c (the C replay of Conduit.hsc's call sequence)
+    compiled against include/lz4frame.h and linked to the PRODUCT library — the reference's conduit driving
+    our LZ4F_* layer.  Returns the path."""
+    out_dir = os.path.join(ROOT, "tests", "_build")
+    out = os.path.join(out_dir, "libreplay_b200.so")
+    srcs = [os.path.join(ROOT, "oracle", "conduit_replay.c"), os.path.join(ROOT, "include", "lz4frame.h")]
+    libdir = os.path.join(ROOT, "lz4-frame-conduit_b200")
+    if not os.path.exists(out) or any(os.path.getmtime(p) > os.path.getmtime(out) for p in srcs):
+        os.makedirs(out_dir, exist_ok=True)
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-DREPLAY_AGAINST_B200", "-I", os.path.join(ROOT, "include"),
+                        "-o", out, srcs[0], "-L", libdir, "-lb200lz4", "-Wl,-rpath," + libdir], check=True)
+    return out
+
+
+@pytest.fixture(scope="session")
+def replay(pkg):
+    """The conduit replay bound to libb200lz4.so's LZ4F_* symbols."""
+    pkg.load()
+    return _bind_replay(C.CDLL(build_replay_b200()))
 
 
 def ref_conduit_decode(lib, frame, cap, chunk=0):

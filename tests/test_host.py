@@ -127,3 +127,76 @@ def test_product_does_not_reference_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", "Makefile")):
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "liboracle" not in txt and "oracle_lz4" not in txt and "orc_" not in txt, os.path.join(dp, f)
+
+
+# ------------------------------------------------------------------ Tier 1: the LZ4F_* symbols Conduit.hsc binds
+LZ4F_SYMBOLS = ["LZ4F_isError", "LZ4F_getErrorName", "LZ4F_createCompressionContext", "LZ4F_freeCompressionContext",
+                "LZ4F_compressBegin", "LZ4F_compressBound", "LZ4F_compressUpdate", "LZ4F_compressEnd",
+                "LZ4F_createDecompressionContext", "LZ4F_freeDecompressionContext", "LZ4F_getFrameInfo",
+                "LZ4F_decompress"]          # Conduit.hsc:150-151,199,181,292,302,311,321,568,545,579,591
+
+
+def test_lz4f_symbols_exported_and_declared(pkg):
+    lib = pkg.load()
+    hdr = open(os.path.join(ROOT, "include", "lz4frame.h")).read()
+    declared = set(re.findall(r"\b(LZ4F_[A-Za-z]+)\s*\(", hdr))
+    assert set(LZ4F_SYMBOLS) <= declared
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+def test_lz4f_struct_layouts_match_reference(replay, ref):
+    # CTypes.hsc:224-232 pokes these structs field by field: sizes 32 / 56
+    assert replay.ref_sizeof_frameinfo() == 32 and replay.ref_sizeof_preferences() == 56
+    if ref is not None:
+        ref.ref_sizeof_frameinfo.restype = ref.ref_sizeof_preferences.restype = C.c_size_t
+        assert ref.ref_sizeof_frameinfo() == 32 and ref.ref_sizeof_preferences() == 56
+
+
+def test_lz4f_contexts_and_header_parse_without_gpu(pkg, manifest):
+    """Context life cycle, LZ4F_compressBound and LZ4F_getFrameInfo are host-only; compute entry points must fail
+    loudly (ERROR_cudaFailure) when no device is usable — there is no CPU codec behind them."""
+    lib = pkg.load()
+    sz = C.c_size_t
+    lib.LZ4F_createDecompressionContext.restype = sz
+    lib.LZ4F_createDecompressionContext.argtypes = [C.POINTER(C.c_void_p), C.c_uint]
+    lib.LZ4F_freeDecompressionContext.restype = sz
+    lib.LZ4F_freeDecompressionContext.argtypes = [C.c_void_p]
+    lib.LZ4F_getFrameInfo.restype = sz
+    lib.LZ4F_getFrameInfo.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.POINTER(sz)]
+    lib.LZ4F_compressBound.restype = sz
+    lib.LZ4F_compressBound.argtypes = [sz, C.c_void_p]
+    lib.LZ4F_getErrorName.restype = C.c_char_p
+    lib.LZ4F_getErrorName.argtypes = [sz]
+    assert lib.LZ4F_freeDecompressionContext(None) == 0                       # lz4frame.c:1081
+    d = C.c_void_p()
+    assert lib.LZ4F_createDecompressionContext(C.byref(d), 100) == 0
+    info = (C.c_uint32 * 8)()
+    frame = golden_bytes(manifest["hellos"]["frames"]["cli"]["file"])
+    n = sz(7)
+    r = lib.LZ4F_getFrameInfo(d, info, frame, C.byref(n))
+    assert r == 4 and n.value == 7
+    want, _ = pkg.frame_header_parse(frame)
+    assert info[0] == want.block_size_id and info[1] == 1 and info[2] == 1    # CLI default: independent, content checksum (lz4io.c:159-175)
+    n = sz(7)
+    assert lib.LZ4F_getFrameInfo(d, info, frame, C.byref(n)) == 4 and n.value == 0   # already decoded: nothing consumed
+    lib.LZ4F_freeDecompressionContext(d)
+    d = C.c_void_p()
+    lib.LZ4F_createDecompressionContext(C.byref(d), 100)
+    n = sz(6)
+    assert lib.LZ4F_getErrorName(lib.LZ4F_getFrameInfo(d, info, frame, C.byref(n))) == b"ERROR_frameHeader_incomplete"
+    n = sz(7)
+    assert lib.LZ4F_getErrorName(lib.LZ4F_getFrameInfo(d, info, b"\x00" * 7, C.byref(n))) == b"ERROR_frameType_unknown"
+    lib.LZ4F_freeDecompressionContext(d)
+    # bound: a batch of buffered input + the call's bytes, all stored, + EndMark + checksum
+    b = lib.LZ4F_compressBound(19 + 16384, None)
+    assert b >= (8 << 20) - 1 + 19 + 16384 + 8 and not pkg.load().b2lz4_is_error(b)
+
+
+def test_lz4f_compress_fails_loudly_without_gpu(replay, pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    out = C.create_string_buffer(64 << 20)
+    r = replay.ref_conduit_compress(b"hello" * 100, 500, out, len(out), 0, 0)
+    assert pkg.load().b2lz4_error_name(r) == b"ERROR_cudaFailure"
