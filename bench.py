@@ -189,7 +189,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--size-mib", type=int, default=1024)
-    ap.add_argument("--sub-log2", type=int, default=18)
+    ap.add_argument("--sub-log2", type=int, default=17)
     ap.add_argument("--no-index", action="store_true", help="plain frames (drop-in default) instead of seekable ones")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")

@@ -211,6 +211,8 @@ struct Cursor {            // what the warp knows about the piece it is decoding
     uint32_t iend_blk;     // end of the owning block's compressed bytes (reference's `iend`)
     uint32_t op, oend;     // current output position / output limit of the owning block (reference's `oend`)
     uint32_t opiece_end;   // exact end of this piece's output (PIECE_EXACT) or == oend
+    uint8_t* win;          // this warp's shared memory: 272-byte window of the compressed stream + 5 link tables of 256 bytes
+    const uint8_t* src_end;// end of the compressed buffer (words that start at or after it are not read)
     uint32_t reach;        // a match at output position m may reach back `m + reach` bytes (mod 2^32):
                            // independent piece: -piece_start;  linked: bytes of earlier output in front of the block
 };
@@ -259,6 +261,7 @@ __device__ __forceinline__ void warp_match(uint8_t* d, uint32_t offset, uint64_t
     }
 }
 
+constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
 constexpr uint32_t LANE_CAP = 32;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
 
 // Decodes one piece.  The warp first WALKS up to 32 sequences (uniform control flow: every lane follows the
@@ -283,12 +286,92 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
     asm volatile("" : "+r"(i_fast), "+r"(o_fast));                          // keep them in registers (no re-derivation per sequence)
     uint32_t err = 0;
     if (pend == ip) return E_decompressionFailed;                           // empty input (lz4.c:1702)
+    // ---- lane-parallel token walk (the common case).  128 consecutive bytes of the stream are examined at once:
+    // every lane computes, for 4 byte positions, where the next token would be IF a token started there (one
+    // shared-memory byte, two with an extension byte).  Squaring that link table four times (T1, T2, T4, T8, T16)
+    // lets lane i jump straight to the i-th token after the known entry point, so 32 sequences are located in a
+    // handful of instructions instead of a 32-step dependent chain of loads.  Anything unusual (a second extension
+    // byte, a literal run that leaves the window, the last 288 input / 560 output bytes of the piece) is marked
+    // WSTOP and goes through the general path below, which carries every acceptance rule of the reference.
+    uint8_t* const win = c.win;
+    uint8_t* const T1 = win + 272, * const T2 = T1 + 256, * const T4 = T2 + 256, * const T8 = T4 + 256, * const T16 = T8 + 256;
+    int32_t wb = 0; bool win_ok = false;                                    // window = stream bytes [wb, wb + 256)
     bool finished = false;
     while (!finished) {
         uint32_t my_a = 0, my_b = 0, my_lit = 0, my_ll = 0, my_ml = 0, my_off = 1;
         bool my_packed = true;
         const uint32_t op0 = op;
         uint32_t n = 0;
+        if (ip < i_fast && op < o_fast) {
+            if (!win_ok || (uint32_t)((int32_t)ip - wb) >= 128u) {
+                // (re)fill the window; its base is 4-byte aligned in memory so that every lane moves whole words
+                wb = (int32_t)ip - (int32_t)((uintptr_t)(sp + ip) & 3u);
+                const uint8_t* g = sp + wb;
+                __syncwarp();
+                const uint32_t w0 = (g + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 4u * lane) : 0u;
+                const uint32_t w1 = (g + 128u + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 128u + 4u * lane) : 0u;
+                ((uint32_t*)win)[lane] = w0; ((uint32_t*)win)[32u + lane] = w1;
+                if (lane < 4u) ((uint32_t*)win)[64u + lane] = 0u;
+                __syncwarp();
+                #pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t p = 32u * k + lane;
+                    const uint32_t t = win[p];
+                    uint32_t ll = t >> 4, q = p + 1u;
+                    bool stop = (wb + (int32_t)p) >= (int32_t)i_fast;
+                    if (ll == 15u) { const uint32_t e = win[q]; ll += e; ++q; stop |= (e == 255u); }
+                    q += ll;
+                    if (q > 250u) { stop = true; q = 250u; }
+                    q += 2u;
+                    if ((t & 15u) == 15u) { const uint32_t e = win[q]; ++q; stop |= (e == 255u); }
+                    T1[p] = (uint8_t)(stop ? WSTOP : q);
+                }
+                __syncwarp();
+                #define B2_SQUARE(TA, TB) { uint8_t r0 = TA[TA[lane]], r1 = TA[TA[32u + lane]], r2 = TA[TA[64u + lane]], r3 = TA[TA[96u + lane]]; \
+                    TB[lane] = r0; TB[32u + lane] = r1; TB[64u + lane] = r2; TB[96u + lane] = r3; __syncwarp(); }
+                B2_SQUARE(T1, T2) B2_SQUARE(T2, T4) B2_SQUARE(T4, T8) B2_SQUARE(T8, T16)
+                #undef B2_SQUARE
+                win_ok = true;
+            }
+            // lane i: the i-th token after the entry point
+            uint32_t x = ip - (uint32_t)wb;
+            if (lane & 1u) x = T1[x];
+            if (lane & 2u) x = T2[x];
+            if (lane & 4u) x = T4[x];
+            if (lane & 8u) x = T8[x];
+            if (lane & 16u) x = T16[x];
+            const uint32_t nxt = T1[x];                                     // entries 128..255 are identity: harmless for x >= 128
+            const bool have = x < 128u && nxt != WSTOP;
+            uint32_t ll = 0, ml = 0, off = 1, lit = 0;
+            if (have) {
+                const uint32_t t = win[x];
+                ll = t >> 4; lit = x + 1u;
+                if (ll == 15u) { ll += win[lit]; ++lit; }
+                const uint32_t q = lit + ll;
+                off = (uint32_t)win[q] | ((uint32_t)win[q + 1u] << 8);
+                ml = (t & 15u) + 4u;
+                if (ml == 19u) ml += win[q + 2u];
+            }
+            const uint32_t nh = (uint32_t)__popc(__ballot_sync(FULL_MASK, have));     // `have` lanes form a prefix
+            const uint32_t sz = (lane < nh) ? ll + ml : 0u;
+            uint32_t run = sz;
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, run, d); if ((int)lane >= d) run += y; }
+            const uint32_t seq_op = op0 + run - sz;                         // where this lane's sequence starts
+            const bool fits = lane < nh && seq_op < o_fast;                 // again a prefix
+            n = (uint32_t)__popc(__ballot_sync(FULL_MASK, fits));
+            if (n) {
+                const bool bad = lane < n && (off == 0u || off > seq_op + ll + reach);           // lz4.c:1977
+                if (__any_sync(FULL_MASK, bad)) { err = E_decompressionFailed; break; }
+                // entry point and output position after the n sequences taken
+                const uint32_t nx_pos = __shfl_sync(FULL_MASK, n < 32u ? x : nxt, n < 32u ? n : 31u);
+                const uint32_t nx_op = __shfl_sync(FULL_MASK, n < 32u ? seq_op : seq_op + sz, n < 32u ? n : 31u);
+                ip = (uint32_t)(wb + (int32_t)nx_pos); op = nx_op;
+                if (lane < n) { my_lit = (uint32_t)(wb + (int32_t)lit); my_ll = ll; my_ml = ml; my_off = off; }
+                my_packed = false;
+            }
+        }
+        if (n == 0)
         for (; n < 32; ++n) {
             if (ip < i_fast && op < o_fast) {
                 const uint32_t token = sp[ip];
@@ -414,6 +497,14 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
     // (streaming decode in batches: lz4frame.c:1286-1349 keeps the same 64 KB)
     if (fi->err != OK) return;
     const uint32_t lane = lane_id();
+    __shared__ __align__(16) uint8_t s_walk[DEC_WARPS][1568];              // per warp: window (272) + 5 link tables (256 each)
+    uint8_t* const my_win = s_walk[threadIdx.x >> 5];
+    for (uint32_t i = lane; i < 5u * 128u; i += 32u) {                       // upper halves of the tables are identity for good
+        const uint32_t t = i >> 7, x = 128u + (i & 127u);
+        my_win[272u + 256u * t + x] = (uint8_t)x;
+    }
+    __syncwarp();
+    const uint8_t* const src_end = src + fi->consumed_with_index;
     const uint32_t n_chains = fi->n_chains;
     const uint32_t block_size = fi->block_size;
     const bool linked = !fi->desc.block_independent;
@@ -444,7 +535,7 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
                 }
             } else {
                 Cursor cu;
-                cu.sp = src + br.src_off; cu.dp = dst + blk_out;
+                cu.sp = src + br.src_off; cu.dp = dst + blk_out; cu.win = my_win; cu.src_end = src_end;
                 cu.ip = (uint32_t)(pc.src_off - br.src_off); cu.iend = cu.ip + pc.src_len;
                 cu.iend_blk = br.csize;
                 const uint32_t op_rel = (uint32_t)(op - blk_out);

@@ -388,7 +388,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 __global__ void __launch_bounds__(1024)
 layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict__ places,
               BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst, uint64_t dst_cap,
-              EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket)
+              EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket, uint8_t* __restrict__ idx_frag)
 {
     __shared__ uint64_t part_bytes[1024];
     __shared__ uint32_t part_chain[1024];
@@ -469,7 +469,9 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
     __syncthreads();
     if (s_res.err != OK) return;
     uint64_t run = part_bytes[tid]; uint32_t rc = part_chain[tid];
-    uint8_t* ib = s_res.index_off ? dst + s_res.index_off + 8 + sizeof(IndexHead) : nullptr;
+    // index entries go into the frame's own index (one-shot call) or, when the frame is produced in chunks, into a
+    // fragment buffer [nb x IndexBlock][n_chains x IndexChain] that the host rebases and concatenates
+    uint8_t* ib = s_res.index_off ? dst + s_res.index_off + 8 + sizeof(IndexHead) : idx_frag;
     uint8_t* ic = ib ? ib + (uint64_t)nb * sizeof(IndexBlock) : nullptr;
     for (uint32_t b = b0; b < b1; ++b) {
         BlockPlace bp = bplaces[b];

@@ -13,6 +13,7 @@
 #include <stddef.h>
 #include <new>
 #include <algorithm>
+#include <vector>
 #include "kernels.h"
 #include "../../include/b200lz4.h"
 
@@ -62,11 +63,16 @@ struct b2lz4_ctx {
     cudaEvent_t ev_in = nullptr, ev_sum = nullptr;
     Small* d_small = nullptr;
     Small* h_small = nullptr;                     // pinned
-    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out, enc_tabs, ring;
+    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out, enc_tabs, ring, idx_frag, stage_in2, stage_out2;
     size_t ring_pos = 0; uint32_t ring_hist = 0;     // streaming linked-block decode: next output offset / valid history bytes
     b2lz4_stats stats{};
     char cuda_err[256] = {0};
     int sm_count = 148;
+    // host-buffer calls cut the stream into chunks and keep several in flight, each on a lane = a child context with
+    // its own stream and workspaces, so that H2D copies, kernels and D2H copies of different chunks overlap
+    b2lz4_ctx* lanes[8] = {};
+    int n_lanes = 0;
+    uint8_t* h_frag = nullptr; size_t h_frag_cap = 0;   // pinned: index fragments of the chunks
 };
 
 namespace {
@@ -89,7 +95,7 @@ void fill_desc(const b2lz4_prefs& p, FrameDesc& d, uint64_t content_size) {
 }
 
 uint32_t sub_size_of(const b2lz4_prefs& p, uint32_t block_size) {
-    uint32_t lg = p.sub_block_log2 ? p.sub_block_log2 : 18u;
+    uint32_t lg = p.sub_block_log2 ? p.sub_block_log2 : 17u;
     lg = std::min(22u, std::max(16u, lg));
     return std::min(block_size, 1u << lg);
 }
@@ -119,7 +125,7 @@ const char* b2lz4_last_cuda_error(const b2lz4_ctx* ctx) { return ctx ? ctx->cuda
 
 void b2lz4_default_prefs(b2lz4_prefs* p) {
     memset(p, 0, sizeof *p);
-    p->block_size_id = 7; p->sub_block_log2 = 18; p->use_index = 1;
+    p->block_size_id = 7; p->sub_block_log2 = 17; p->use_index = 1;
     // write_index stays 0: the stock lz4 CLI cannot skip a skippable frame on a pipe (lz4io.c:1124-1133 uses fseek),
     // so plain frames are the drop-in default and the seekable index is opt-in.
 }
@@ -196,13 +202,15 @@ size_t b2lz4_create(b2lz4_ctx** out, int device, const b2lz4_prefs* prefs) {
 
 size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (!ctx) return 0;
+    for (auto& l : ctx->lanes) { b2lz4_destroy(l); l = nullptr; }
     cudaSetDevice(ctx->device);
     if (ctx->st) cudaStreamSynchronize(ctx->st);
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
-                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring }) b->release();
+                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2 }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
     for (auto& v : ctx->ev) if (v) cudaEventDestroy(v);
     if (ctx->ev_in) cudaEventDestroy(ctx->ev_in);
     if (ctx->ev_sum) cudaEventDestroy(ctx->ev_sum);
@@ -236,7 +244,7 @@ void b2lz4_pinned_free(void* p) { if (p) cudaFreeHost(p); }
 // -------------------------------------------------------------------------------------- compress
 // Launch sequence on ctx->st: find_emit -> layout -> gather -> [block checksums] ; the content checksum
 // runs on ctx->st2 over the input, concurrently, and its digest is stored once layout knows the offset.
-enum : unsigned { CL_WHOLE_FRAME = 1u, CL_SUM_RESET = 2u, CL_SUM_UPDATE = 4u };
+enum : unsigned { CL_WHOLE_FRAME = 1u, CL_SUM_RESET = 2u, CL_SUM_UPDATE = 4u, CL_INDEX_FRAGMENT = 8u };
 static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, uint8_t* d_dst, size_t cap,
                               unsigned flags)
 {
@@ -265,6 +273,7 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     CU(ctx->subs.ensure((size_t)P.n_subs * sizeof(SubOut)));
     CU(ctx->places.ensure((size_t)P.n_subs * sizeof(SubPlace)));
     CU(ctx->bplaces.ensure((size_t)P.n_blocks * sizeof(BlockPlace)));
+    if (flags & CL_INDEX_FRAGMENT) CU(ctx->idx_frag.ensure((size_t)P.n_blocks * sizeof(IndexBlock) + (size_t)P.n_subs * sizeof(IndexChain) + 64));
 
     Small* ds = ctx->d_small;
     uint32_t launches = 0;
@@ -286,7 +295,8 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     }
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
     layout_kernel<<<1, 1024, 0, ctx->st>>>(P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p,
-                                           (BlockPlace*)ctx->bplaces.p, d_dst, cap, &ds->eres, &ds->ticket_enc);
+                                           (BlockPlace*)ctx->bplaces.p, d_dst, cap, &ds->eres, &ds->ticket_enc,
+                                           (flags & CL_INDEX_FRAGMENT) ? (uint8_t*)ctx->idx_frag.p : nullptr);
     ++launches;
     if (P.n_subs) {
         uint32_t grid = std::min<uint32_t>(P.n_subs, (uint32_t)ctx->sm_count * 8u);
@@ -379,25 +389,36 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
 static_assert(offsetof(Small, dres) == sizeof(FrameIndex), "fi and dres must be contiguous for the single copy");
 
 static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed,
-                                     uint32_t hist, uint32_t mode0 = 0u);
+                                     uint32_t hist, uint32_t mode0 = 0u, bool launched0 = false);
+static uint32_t tables_for(size_t n, size_t cap) {
+    return (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, std::max<uint64_t>(4096, (n >> 12) + (cap >> 16) + 64));
+}
+// queues the first decode attempt on ctx->st without waiting; decompress_device_impl(..., launched0 = true) completes it
+static size_t decompress_begin(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, uint32_t hist, uint32_t mode0) {
+    ctx->stats = b2lz4_stats{};
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u);
+    return decompress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, mode, tables_for(n, cap), hist);
+}
 size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed) {
     return decompress_device_impl(ctx, d_src, n, d_dst, cap, consumed, 0u);
 }
 static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed,
-                                     uint32_t hist, uint32_t mode0) {
+                                     uint32_t hist, uint32_t mode0, bool launched0) {
     if (consumed) *consumed = 0;
     if (!ctx || !d_src || (!d_dst && cap)) return err_code(E_GENERIC);
     if (n < (size_t)HEADER_MIN) return err_code(E_frameHeader_incomplete);
     size_t r = set_device(ctx); if (r) return r;
-    ctx->stats = b2lz4_stats{};
+    if (!launched0) ctx->stats = b2lz4_stats{};
     static uint8_t* dummy = nullptr;
     uint8_t* dst = (uint8_t*)d_dst;
     if (!dst) { if (!dummy) CU(cudaMalloc(&dummy, 256)); dst = dummy; }
     uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u);
-    uint32_t cap_tables = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, std::max<uint64_t>(4096, (n >> 12) + (cap >> 16) + 64));
+    uint32_t cap_tables = tables_for(n, cap);
     for (int attempt = 0; attempt < 4; ++attempt) {
-        r = decompress_launch(ctx, (const uint8_t*)d_src, n, dst, cap, mode, cap_tables, hist);
-        if (r) return r;
+        if (!(launched0 && attempt == 0)) {
+            r = decompress_launch(ctx, (const uint8_t*)d_src, n, dst, cap, mode, cap_tables, hist);
+            if (r) return r;
+        }
         CU(cudaStreamSynchronize(ctx->st));
         const FrameIndex& fi = ctx->h_small->fi;
         const DecodeResult& dr = ctx->h_small->dres;
@@ -427,30 +448,151 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
 }
 
 // -------------------------------------------------------------------------------------- host buffers
+// pipeline shape of the host-buffer calls: B2LZ4_LANES chunks in flight (default 4), B2LZ4_PIPE_MB per chunk (default: an
+// eighth of the stream, 32..256 MiB)
+static int pipe_lanes() { const char* e = getenv("B2LZ4_LANES"); int v = e ? atoi(e) : 4; return std::min(8, std::max(1, v)); }
+static size_t pipe_chunk(size_t n, size_t block_size) {
+    const char* e = getenv("B2LZ4_PIPE_MB");
+    size_t c = e ? (size_t)std::max(1, atoi(e)) << 20 : std::min<size_t>(256u << 20, std::max<size_t>(32u << 20, n / 8));
+    c = std::max(block_size, c / block_size * block_size);
+    return c;
+}
+static size_t ensure_lanes(b2lz4_ctx* ctx, int want) {
+    for (int k = ctx->n_lanes; k < want; ++k) {
+        size_t r = b2lz4_create(&ctx->lanes[k], ctx->device, &ctx->prefs);
+        if (b2lz4_is_error(r)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "lane context creation failed"); return r; }
+        ctx->n_lanes = k + 1;
+    }
+    for (int k = 0; k < ctx->n_lanes; ++k) ctx->lanes[k]->prefs = ctx->prefs;
+    return 0;
+}
+#define LANE_CU(L, call)                                                                           \
+    do { cudaError_t e_ = (call);                                                                  \
+         if (e_ != cudaSuccess) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s: %s (%s:%d)", #call, \
+                                           cudaGetErrorString(e_), __FILE__, __LINE__);            \
+                                  cudaGetLastError(); return err_code(E_cudaFailure); } } while (0)
+
+// One frame from a host buffer.  The stream is cut into chunks of whole blocks; chunk i goes to lane i mod L:
+// H2D copy -> match finder / layout / gather on the lane's stream, no host wait; chunks are completed in order
+// (their compressed size decides where the next one lands in dst) and copied back while later chunks still run.
 size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap) {
     if (!ctx || (!src && n) || !dst) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
     ctx->stats = b2lz4_stats{};
-    size_t bound = b2lz4_compress_bound(n, &ctx->prefs);
-    CU(ctx->stage_in.ensure(n + 16));
-    CU(ctx->stage_out.ensure(bound + 16));
-    CU(cudaEventRecord(ctx->ev[4], ctx->st));
-    if (n) CU(cudaMemcpyAsync(ctx->stage_in.p, src, n, cudaMemcpyHostToDevice, ctx->st));
-    CU(cudaEventRecord(ctx->ev[5], ctx->st));
-    r = compress_launch(ctx, (const uint8_t*)ctx->stage_in.p, n, (uint8_t*)ctx->stage_out.p, std::min(bound, cap), CL_WHOLE_FRAME | CL_SUM_RESET | CL_SUM_UPDATE);
-    if (r) return r;
-    r = compress_finish(ctx, n);
-    if (b2lz4_is_error(r)) return r;
-    CU(cudaEventRecord(ctx->ev[6], ctx->st));
-    CU(cudaMemcpyAsync(dst, ctx->stage_out.p, r, cudaMemcpyDeviceToHost, ctx->st));
-    CU(cudaEventRecord(ctx->ev[7], ctx->st));
+    const b2lz4_prefs pr = ctx->prefs;
+    const size_t bs = block_size_of(pr.block_size_id ? pr.block_size_id : 7u);
+    const size_t chunk = pipe_chunk(n, bs);
+    const size_t nchunks = n ? (n + chunk - 1) / chunk : 0;
+    const int L = (int)std::min<size_t>((size_t)pipe_lanes(), std::max<size_t>(1, nchunks));
+    r = ensure_lanes(ctx, L); if (r) return r;
+    uint8_t* out = (uint8_t*)dst;
+    size_t o = b2lz4_frame_header_write(out, cap, &pr, n);
+    if (b2lz4_is_error(o)) return o;
+    const bool sum = pr.content_checksum != 0, want_index = pr.write_index != 0;
+    Small* ds = ctx->d_small;
+    if (sum) xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh);
+    std::vector<uint8_t> ix_blocks, ix_chains;             // index entries gathered from the chunks
+    struct Frag { size_t off; uint32_t nb, nc, chain_base; };
+    std::vector<Frag> frags;
+    size_t frag_used = 0;
+    if (want_index) {                                      // pinned landing area for the chunks' index fragments
+        const size_t ss = sub_size_of(pr, (uint32_t)bs);
+        const size_t need = (n / bs + nchunks + 2) * sizeof(IndexBlock) + (n / ss + 2 * nchunks + n / bs + 2) * sizeof(IndexChain);
+        if (need > ctx->h_frag_cap) {
+            if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
+            ctx->h_frag = nullptr; ctx->h_frag_cap = 0;
+            CU(cudaMallocHost(&ctx->h_frag, need + need / 4));
+            ctx->h_frag_cap = need + need / 4;
+        }
+    }
+    uint32_t chains_total = 0, blocks_total = 0, launches = sum ? 1u : 0u;
+    float ms_main = 0, ms_total = 0;
+    cudaEvent_t t0 = ctx->ev[4], t1 = ctx->ev[5];
+    CU(cudaEventRecord(t0, ctx->st));
+
+    auto submit = [&](size_t i) -> size_t {
+        b2lz4_ctx* ln = ctx->lanes[i % L];
+        const size_t off = i * chunk, len = std::min(chunk, n - off);
+        LANE_CU(ln, cudaSetDevice(ctx->device));
+        LANE_CU(ln, ln->stage_in.ensure(len + 16));
+        LANE_CU(ln, ln->stage_out.ensure(b2lz4_compress_bound(len, &pr) + 16));
+        if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // the checksum pass of the lane's previous chunk
+        LANE_CU(ln, cudaMemcpyAsync(ln->stage_in.p, (const uint8_t*)src + off, len, cudaMemcpyHostToDevice, ln->st));
+        if (sum) {                                                              // serial XXH32 in stream order on the parent's 2nd stream
+            LANE_CU(ln, cudaEventRecord(ln->ev_in, ln->st));
+            LANE_CU(ln, cudaStreamWaitEvent(ctx->st2, ln->ev_in, 0));
+            xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>((const uint8_t*)ln->stage_in.p, len, nullptr, nullptr, &ds->xxh);
+            LANE_CU(ln, cudaEventRecord(ln->ev_sum, ctx->st2));
+            ++launches;
+        }
+        ln->stats = b2lz4_stats{};
+        size_t e = compress_launch(ln, (const uint8_t*)ln->stage_in.p, len, (uint8_t*)ln->stage_out.p, ln->stage_out.cap,
+                                   want_index ? CL_INDEX_FRAGMENT : 0u);
+        if (e) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return e; }
+        return 0;
+    };
+    auto complete = [&](size_t i) -> size_t {
+        b2lz4_ctx* ln = ctx->lanes[i % L];
+        const size_t off = i * chunk, len = std::min(chunk, n - off);
+        size_t c = compress_finish(ln, len);                                    // waits for the lane
+        if (b2lz4_is_error(c)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return c; }
+        if (o + c + 8 > cap) return err_code(E_dstMaxSize_tooSmall);
+        LANE_CU(ln, cudaMemcpyAsync(out + o, ln->stage_out.p, c, cudaMemcpyDeviceToHost, ln->st));
+        const EncodeResult& er = ln->h_small->eres;
+        if (want_index) {                                                       // fragment: [nb x IndexBlock][n_chains x IndexChain], chunk-relative
+            const size_t fb = er.n_blocks * sizeof(IndexBlock) + er.n_chains * sizeof(IndexChain);
+            if (frag_used + fb > ctx->h_frag_cap) return err_code(E_GENERIC);
+            LANE_CU(ln, cudaMemcpyAsync(ctx->h_frag + frag_used, ln->idx_frag.p, fb, cudaMemcpyDeviceToHost, ln->st));
+            frags.push_back({frag_used, er.n_blocks, er.n_chains, chains_total});
+            frag_used += fb;
+        }
+        chains_total += er.n_chains; blocks_total += er.n_blocks;
+        launches += ln->stats.kernel_launches; ms_main += ln->stats.ms_main; ms_total += ln->stats.ms_total;
+        o += c;
+        return 0;
+    };
+    for (size_t i = 0; i < nchunks; ++i) {
+        if (i >= (size_t)L) { r = complete(i - L); if (r) return r; }
+        r = submit(i); if (r) return r;
+    }
+    for (size_t i = nchunks > (size_t)L ? nchunks - L : 0; i < nchunks; ++i) { r = complete(i); if (r) return r; }
+    for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st));
+
+    // EndMark, content checksum, index frame: a few bytes, written by the host (lz4frame.c:998-1007)
+    if (o + 4 + (sum ? 4u : 0u) > cap) return err_code(E_dstMaxSize_tooSmall);
+    st_le32(out + o, 0u); o += 4;
+    if (sum) { uint32_t h = 0; r = b2lz4_content_checksum(ctx, &h); if (r) return r; st_le32(out + o, h); o += 4; ++launches; }
+    if (want_index) {
+        for (const Frag& f : frags) {                                           // rebase chain numbers, concatenate
+            IndexBlock* ib = (IndexBlock*)(ctx->h_frag + f.off);
+            for (uint32_t k = 0; k < f.nb; ++k) ib[k].first_chain += f.chain_base;
+            const uint8_t* p = ctx->h_frag + f.off;
+            ix_blocks.insert(ix_blocks.end(), p, p + f.nb * sizeof(IndexBlock));
+            ix_chains.insert(ix_chains.end(), p + f.nb * sizeof(IndexBlock), p + f.nb * sizeof(IndexBlock) + f.nc * sizeof(IndexChain));
+        }
+        const uint32_t pb = (uint32_t)(sizeof(IndexHead) + ix_blocks.size() + ix_chains.size());
+        if (o + 16 + pb > cap) return err_code(E_dstMaxSize_tooSmall);
+        uint8_t* x = out + o;
+        st_le32(x, IDX_SKIP_MAGIC); st_le32(x + 4, pb + 8u); x += 8;
+        IndexHead h{}; h.magic = IDX_MAGIC; h.version = 1; h.block_size = (uint32_t)bs; h.n_blocks = blocks_total;
+        h.n_chains = chains_total; h.reserved = 0; h.content_size = n;
+        memcpy(x, &h, sizeof h); x += sizeof h;
+        if (!ix_blocks.empty()) memcpy(x, ix_blocks.data(), ix_blocks.size());
+        x += ix_blocks.size();
+        if (!ix_chains.empty()) memcpy(x, ix_chains.data(), ix_chains.size());
+        x += ix_chains.size();
+        st_le32(x, pb); st_le32(x + 4, IDX_MAGIC);
+        o += 16 + pb;
+    }
+    CU(cudaEventRecord(t1, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
-    cudaEventElapsedTime(&ctx->stats.ms_h2d, ctx->ev[4], ctx->ev[5]);
-    cudaEventElapsedTime(&ctx->stats.ms_d2h, ctx->ev[6], ctx->ev[7]);
-    return r;
+    ctx->stats.n_blocks = blocks_total; ctx->stats.n_chains = chains_total; ctx->stats.indexed = want_index ? 1u : 0u;
+    ctx->stats.kernel_launches = launches; ctx->stats.ms_main = ms_main; ctx->stats.ms_total = ms_total;
+    ctx->stats.bytes_in = n; ctx->stats.bytes_out = o;
+    return o;
 }
 
-size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, size_t* consumed) {
+static size_t decompress_host_whole(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, size_t* consumed) {
     if (consumed) *consumed = 0;
     if (!ctx || !src || (!dst && cap)) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
@@ -469,6 +611,163 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* ds
     cudaEventElapsedTime(&ctx->stats.ms_h2d, e0, e1);
     cudaEventElapsedTime(&ctx->stats.ms_d2h, e2, e3);
     return r;
+}
+
+// what the host learns from walking the block header words of a frame that lies in host memory
+struct HostFrame {
+    FrameDesc desc{};
+    uint32_t block_size = 0;
+    struct Blk { size_t off; uint32_t word; };       // offset of the header word, the word itself
+    std::vector<Blk> blocks;
+    size_t end_blocks = 0;                           // offset of the EndMark
+    size_t consumed = 0;                             // through EndMark (+ content checksum) (+ index frame when used)
+    uint32_t stored_sum = 0;
+    const uint8_t* ix_blocks = nullptr; const uint8_t* ix_chains = nullptr;   // validated index payload, or null
+    uint32_t ix_nchains = 0;
+};
+
+// false = leave it to the device scan (which reports the precise error)
+static bool host_scan(const uint8_t* src, size_t n, bool use_index, HostFrame& f) {
+    if (header_parse(src, n, f.desc) != OK) return false;
+    f.block_size = block_size_of(f.desc.block_size_id);
+    const uint32_t bc = f.desc.block_checksum ? 4u : 0u;
+    size_t ip = f.desc.header_size;
+    for (;;) {
+        if (n - ip < 4) return false;
+        const uint32_t w = ld_le32(src + ip);
+        const uint32_t cs = w & 0x7FFFFFFFu;
+        if (cs == 0) break;
+        if (cs > f.block_size || n - ip - 4 < (size_t)cs + bc) return false;
+        f.blocks.push_back({ip, w});
+        ip += 4 + (size_t)cs + bc;
+    }
+    f.end_blocks = ip; ip += 4;
+    if (f.desc.content_checksum) { if (n - ip < 4) return false; f.stored_sum = ld_le32(src + ip); ip += 4; }
+    f.consumed = ip;
+    if (use_index && f.desc.block_independent && n - ip >= 16 + sizeof(IndexHead) && ld_le32(src + ip) == IDX_SKIP_MAGIC) {
+        const uint32_t sz = ld_le32(src + ip + 4);
+        if (sz >= 8 + sizeof(IndexHead) && n - ip - 8 >= sz) {
+            const uint8_t* pl = src + ip + 8; const uint32_t pb = sz - 8;
+            IndexHead h; memcpy(&h, pl, sizeof h);
+            const uint64_t want = sizeof(IndexHead) + (uint64_t)h.n_blocks * sizeof(IndexBlock) + (uint64_t)h.n_chains * sizeof(IndexChain);
+            if (h.magic == IDX_MAGIC && h.version == 1 && want == pb && h.block_size == f.block_size &&
+                h.n_blocks == f.blocks.size() && ld_le32(pl + pb) == pb && ld_le32(pl + pb + 4) == IDX_MAGIC) {
+                f.ix_blocks = pl + sizeof(IndexHead); f.ix_chains = f.ix_blocks + (size_t)h.n_blocks * sizeof(IndexBlock);
+                f.ix_nchains = h.n_chains;
+                f.consumed = ip + 8 + sz;
+            }
+        }
+    }
+    return true;
+}
+
+// One frame from a host buffer.  Independent-block frames are cut into groups of whole blocks on the host (a serial walk
+// over the 4-byte header words); group g goes to lane g mod L as a small frame of its own — header, the blocks, an EndMark
+// and the group's slice of the index — so that its H2D copy, decode and D2H copy overlap with the other lanes'.
+size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* dst, size_t cap, size_t* consumed) {
+    if (consumed) *consumed = 0;
+    if (!ctx || !src_ || (!dst && cap)) return err_code(E_GENERIC);
+    size_t r = set_device(ctx); if (r) return r;
+    const uint8_t* src = (const uint8_t*)src_;
+    HostFrame f;
+    const bool ok = n >= (size_t)HEADER_MIN && host_scan(src, n, ctx->prefs.use_index != 0, f);
+    const size_t per_group = ok && f.block_size ? std::max<size_t>(1, pipe_chunk((size_t)f.blocks.size() * f.block_size, f.block_size) / f.block_size) : 0;
+    if (!ok || !f.desc.block_independent || f.blocks.size() <= per_group)
+        return decompress_host_whole(ctx, src_, n, dst, cap, consumed);           // linked frames, small frames, anything odd
+    ctx->stats = b2lz4_stats{};
+    const size_t nb = f.blocks.size(), ngroups = (nb + per_group - 1) / per_group;
+    const int L = (int)std::min<size_t>((size_t)pipe_lanes(), ngroups);
+    r = ensure_lanes(ctx, L); if (r) return r;
+    const uint32_t bc = f.desc.block_checksum ? 4u : 0u;
+    const bool sum = f.desc.content_checksum != 0;
+    Small* ds = ctx->d_small;
+    if (sum) xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh);
+    FrameDesc gd{}; gd.block_size_id = f.desc.block_size_id; gd.block_independent = 1; gd.block_checksum = f.desc.block_checksum;
+    uint8_t ghdr[HEADER_MAX]; const uint32_t ghs = header_write(ghdr, gd);
+    uint8_t* out = (uint8_t*)dst;
+    size_t o = 0;
+    uint32_t launches = 0, chains_total = 0; float ms_main = 0, ms_total = 0;
+    struct Group { size_t src_len, frame_len, out_cap; };
+    std::vector<Group> groups(ngroups);
+
+    auto submit = [&](size_t g) -> size_t {
+        b2lz4_ctx* ln = ctx->lanes[g % L];
+        const size_t b0 = g * per_group, b1 = std::min(nb, b0 + per_group);
+        const size_t s0 = f.blocks[b0].off, s1 = b1 < nb ? f.blocks[b1].off : f.end_blocks;
+        (void)bc;
+        // the group's slice of the index, rebased: [skip magic, size][IndexHead][blocks][chains][size, magic]
+        std::vector<uint8_t> ix;
+        if (f.ix_blocks) {
+            const IndexBlock* ib = (const IndexBlock*)f.ix_blocks;
+            IndexBlock first; memcpy(&first, ib + b0, sizeof first);
+            IndexBlock last; memcpy(&last, ib + (b1 - 1), sizeof last);
+            const uint32_t c0 = first.first_chain, c1 = last.first_chain + last.n_chain;
+            if (c1 < c0 || c1 > f.ix_nchains) return err_code(E_GENERIC);
+            const uint32_t pb = (uint32_t)(sizeof(IndexHead) + (b1 - b0) * sizeof(IndexBlock) + (size_t)(c1 - c0) * sizeof(IndexChain));
+            ix.resize(16 + pb);
+            uint8_t* x = ix.data();
+            st_le32(x, IDX_SKIP_MAGIC); st_le32(x + 4, pb + 8u); x += 8;
+            IndexHead h{}; h.magic = IDX_MAGIC; h.version = 1; h.block_size = f.block_size; h.n_blocks = (uint32_t)(b1 - b0); h.n_chains = c1 - c0;
+            uint64_t usum = 0;
+            IndexBlock* ob = (IndexBlock*)(x + sizeof h);
+            for (size_t k = b0; k < b1; ++k) { IndexBlock e; memcpy(&e, ib + k, sizeof e); usum += e.usize; e.first_chain -= c0; memcpy(ob + (k - b0), &e, sizeof e); }
+            h.content_size = usum;
+            memcpy(x, &h, sizeof h);
+            memcpy(x + sizeof h + (b1 - b0) * sizeof(IndexBlock), f.ix_chains + (size_t)c0 * sizeof(IndexChain), (size_t)(c1 - c0) * sizeof(IndexChain));
+            st_le32(x + pb, pb); st_le32(x + pb + 4, IDX_MAGIC);
+        }
+        Group& G = groups[g];
+        G.src_len = s1 - s0; G.frame_len = ghs + G.src_len + 4 + ix.size(); G.out_cap = (b1 - b0) * (size_t)f.block_size;
+        LANE_CU(ln, cudaSetDevice(ctx->device));
+        LANE_CU(ln, ln->stage_in.ensure(G.frame_len + 16));
+        LANE_CU(ln, ln->stage_out.ensure(G.out_cap + 16));
+        if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // checksum pass over the lane's previous output
+        uint8_t* din = (uint8_t*)ln->stage_in.p;
+        const uint32_t zero = 0;
+        LANE_CU(ln, cudaMemcpyAsync(din, ghdr, ghs, cudaMemcpyHostToDevice, ln->st));
+        LANE_CU(ln, cudaMemcpyAsync(din + ghs, src + s0, G.src_len, cudaMemcpyHostToDevice, ln->st));
+        LANE_CU(ln, cudaMemcpyAsync(din + ghs + G.src_len, &zero, 4, cudaMemcpyHostToDevice, ln->st));
+        if (!ix.empty()) LANE_CU(ln, cudaMemcpyAsync(din + ghs + G.src_len + 4, ix.data(), ix.size(), cudaMemcpyHostToDevice, ln->st));
+        ln->prefs.use_index = f.ix_blocks ? 1u : 0u;
+        size_t e = decompress_begin(ln, din, G.frame_len, ln->stage_out.p, G.out_cap, 0u, SCAN_BATCH);
+        if (e) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return e; }
+        return 0;
+    };
+    auto complete = [&](size_t g) -> size_t {
+        b2lz4_ctx* ln = ctx->lanes[g % L];
+        const Group& G = groups[g];
+        size_t used = 0;
+        size_t c = decompress_device_impl(ln, ln->stage_in.p, G.frame_len, ln->stage_out.p, G.out_cap, &used, 0u, SCAN_BATCH, true);
+        if (b2lz4_is_error(c)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return c; }
+        if (used != G.frame_len) return err_code(E_decompressionFailed);
+        if (o + c > cap) return err_code(E_dstMaxSize_tooSmall);
+        if (c) LANE_CU(ln, cudaMemcpyAsync(out + o, ln->stage_out.p, c, cudaMemcpyDeviceToHost, ln->st));
+        if (sum && c) {
+            xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>((const uint8_t*)ln->stage_out.p, c, nullptr, nullptr, &ds->xxh);
+            LANE_CU(ln, cudaEventRecord(ln->ev_sum, ctx->st2));
+            ++launches;
+        }
+        launches += ln->stats.kernel_launches; ms_main += ln->stats.ms_main; ms_total += ln->stats.ms_total;
+        chains_total += ln->stats.n_chains;
+        o += c;
+        return 0;
+    };
+    for (size_t g = 0; g < ngroups; ++g) {
+        if (g >= (size_t)L) { r = complete(g - L); if (r) return r; }
+        r = submit(g); if (r) return r;
+    }
+    for (size_t g = ngroups > (size_t)L ? ngroups - L : 0; g < ngroups; ++g) { r = complete(g); if (r) return r; }
+    for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st));
+    if (sum) {
+        uint32_t h = 0; r = b2lz4_content_checksum(ctx, &h); if (r) return r;
+        if (h != f.stored_sum) return err_code(E_contentChecksum_invalid);      // lz4frame.c:1734-1745
+    }
+    if (f.desc.has_content_size && f.desc.content_size != o) return err_code(E_frameSize_wrong);   // lz4frame.c:1715-1716
+    ctx->stats.n_blocks = (uint32_t)nb; ctx->stats.n_chains = chains_total; ctx->stats.indexed = f.ix_blocks ? 1u : 0u;
+    ctx->stats.kernel_launches = launches; ctx->stats.ms_main = ms_main; ctx->stats.ms_total = ms_total;
+    ctx->stats.bytes_in = n; ctx->stats.bytes_out = o;
+    if (consumed) *consumed = f.consumed;
+    return o;
 }
 
 // -------------------------------------------------------------------------------------- streaming (batches of blocks)

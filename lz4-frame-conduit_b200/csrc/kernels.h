@@ -38,7 +38,7 @@ __global__ void verify_block_checksums_kernel(const uint8_t* src, const FrameInd
 __global__ void find_emit_kernel(const uint8_t* src, EncParams P, uint8_t* scratch, SubOut* subs, uint32_t* ticket, uint16_t* gtab);
 size_t find_emit_gtab_bytes(uint32_t grid);
 __global__ void layout_kernel(EncParams P, const SubOut* subs, SubPlace* places, BlockPlace* bplaces,
-                              uint8_t* dst, uint64_t dst_cap, EncodeResult* res, uint32_t* ticket);
+                              uint8_t* dst, uint64_t dst_cap, EncodeResult* res, uint32_t* ticket, uint8_t* idx_frag);
 __global__ void gather_kernel(const uint8_t* src, EncParams P, const uint8_t* scratch, const SubOut* subs,
                               const SubPlace* places, const BlockPlace* bplaces, uint8_t* dst,
                               const EncodeResult* res);
