@@ -19,7 +19,10 @@ constexpr int DEC_WARPS = 4;          // warps per CTA in the sequence decoder
 constexpr int ENC_WARPS = B2_ENC_WARPS;          // warps per CTA in the match finder (one hash table each)
 constexpr int ENC_SMEM_WARPS = B2_ENC_SMEM_WARPS;     // ... of which this many keep their table in shared memory; the others use a global (L1/L2) table
 constexpr int ENC_CTAS_PER_SM = B2_ENC_CTAS;   // resident CTAs per SM the kernel is built for
-constexpr int ENC_HLOG  = 13;         // 8192-entry u16 hash table per warp (16 KB)
+#ifndef B2_ENC_HLOG
+#define B2_ENC_HLOG 13
+#endif
+constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 8192-entry u16 hash table per warp (16 KB)
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u };
 
 // ---- decode
