@@ -262,7 +262,10 @@ __device__ __forceinline__ void warp_match(uint8_t* d, uint32_t offset, uint64_t
 }
 
 constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
-constexpr uint32_t LANE_CAP = 32;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
+#ifndef B2_DEC_LANE_CAP
+#define B2_DEC_LANE_CAP 32
+#endif
+constexpr uint32_t LANE_CAP = B2_DEC_LANE_CAP;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
 
 // Decodes one piece.  The warp first WALKS up to 32 sequences (uniform control flow: every lane follows the
 // token chain, lane i keeps the fields of sequence i), then copies them lane-parallel: literals of all 32
@@ -299,76 +302,89 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
     bool finished = false;
     while (!finished) {
         uint32_t my_a = 0, my_b = 0, my_lit = 0, my_ll = 0, my_ml = 0, my_off = 1;
-        bool my_packed = true;
+        bool my_packed = true, fast_batch = false;
+        uint32_t my_op_fast = 0;
         const uint32_t op0 = op;
         uint32_t n = 0;
         if (ip < i_fast && op < o_fast) {
-            if (!win_ok || (uint32_t)((int32_t)ip - wb) >= 128u) {
-                // (re)fill the window; its base is 4-byte aligned in memory so that every lane moves whole words
-                wb = (int32_t)ip - (int32_t)((uintptr_t)(sp + ip) & 3u);
-                const uint8_t* g = sp + wb;
-                __syncwarp();
-                const uint32_t w0 = (g + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 4u * lane) : 0u;
-                const uint32_t w1 = (g + 128u + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 128u + 4u * lane) : 0u;
-                ((uint32_t*)win)[lane] = w0; ((uint32_t*)win)[32u + lane] = w1;
-                if (lane < 4u) ((uint32_t*)win)[64u + lane] = 0u;
-                __syncwarp();
-                #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t p = 32u * k + lane;
-                    const uint32_t t = win[p];
-                    uint32_t ll = t >> 4, q = p + 1u;
-                    bool stop = (wb + (int32_t)p) >= (int32_t)i_fast;
-                    if (ll == 15u) { const uint32_t e = win[q]; ll += e; ++q; stop |= (e == 255u); }
-                    q += ll;
-                    if (q > 250u) { stop = true; q = 250u; }
-                    q += 2u;
-                    if ((t & 15u) == 15u) { const uint32_t e = win[q]; ++q; stop |= (e == 255u); }
-                    T1[p] = (uint8_t)(stop ? WSTOP : q);
+            // gather up to 32 sequences, refilling the window as often as needed: lanes n.. take the tokens that follow `tip`
+            uint32_t tip = ip, my_tok = 0, my_nxt = 0, ll = 0, ml = 0, off = 1, lit = 0;
+            while (tip < i_fast) {
+                if (!win_ok || (uint32_t)((int32_t)tip - wb) >= 128u) {
+                    // (re)fill the window; its base is 4-byte aligned in memory so that every lane moves whole words
+                    wb = (int32_t)tip - (int32_t)((uintptr_t)(sp + tip) & 3u);
+                    const uint8_t* g = sp + wb;
+                    __syncwarp();
+                    const uint32_t w0 = (g + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 4u * lane) : 0u;
+                    const uint32_t w1 = (g + 128u + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 128u + 4u * lane) : 0u;
+                    ((uint32_t*)win)[lane] = w0; ((uint32_t*)win)[32u + lane] = w1;
+                    if (lane < 4u) ((uint32_t*)win)[64u + lane] = 0u;
+                    __syncwarp();
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t p = 32u * k + lane;
+                        const uint32_t t = win[p];
+                        uint32_t l2 = t >> 4, q = p + 1u;
+                        bool stop = (wb + (int32_t)p) >= (int32_t)i_fast;
+                        if (l2 == 15u) { const uint32_t e = win[q]; l2 += e; ++q; stop |= (e == 255u); }
+                        q += l2;
+                        if (q > 250u) { stop = true; q = 250u; }
+                        q += 2u;
+                        if ((t & 15u) == 15u) { const uint32_t e = win[q]; ++q; stop |= (e == 255u); }
+                        T1[p] = (uint8_t)(stop ? WSTOP : q);
+                    }
+                    __syncwarp();
+                    #define B2_SQUARE(TA, TB) { uint8_t r0 = TA[TA[lane]], r1 = TA[TA[32u + lane]], r2 = TA[TA[64u + lane]], r3 = TA[TA[96u + lane]]; \
+                        TB[lane] = r0; TB[32u + lane] = r1; TB[64u + lane] = r2; TB[96u + lane] = r3; __syncwarp(); }
+                    B2_SQUARE(T1, T2) B2_SQUARE(T2, T4) B2_SQUARE(T4, T8) B2_SQUARE(T8, T16)
+                    #undef B2_SQUARE
+                    win_ok = true;
                 }
-                __syncwarp();
-                #define B2_SQUARE(TA, TB) { uint8_t r0 = TA[TA[lane]], r1 = TA[TA[32u + lane]], r2 = TA[TA[64u + lane]], r3 = TA[TA[96u + lane]]; \
-                    TB[lane] = r0; TB[32u + lane] = r1; TB[64u + lane] = r2; TB[96u + lane] = r3; __syncwarp(); }
-                B2_SQUARE(T1, T2) B2_SQUARE(T2, T4) B2_SQUARE(T4, T8) B2_SQUARE(T8, T16)
-                #undef B2_SQUARE
-                win_ok = true;
+                // lane n + i: the i-th token after `tip`
+                const uint32_t kx = lane - n;                                   // lanes below n already hold a sequence
+                uint32_t x = tip - (uint32_t)wb;
+                if (kx & 1u) x = T1[x];
+                if (kx & 2u) x = T2[x];
+                if (kx & 4u) x = T4[x];
+                if (kx & 8u) x = T8[x];
+                if (kx & 16u) x = T16[x];
+                const uint32_t nxt = T1[x];                                     // entries 128..255 are identity: harmless for x >= 128
+                const bool have = lane >= n && x < 128u && nxt != WSTOP;
+                if (have) {
+                    const uint32_t t = win[x];
+                    ll = t >> 4; lit = x + 1u;
+                    if (ll == 15u) { ll += win[lit]; ++lit; }
+                    const uint32_t q = lit + ll;
+                    off = (uint32_t)win[q] | ((uint32_t)win[q + 1u] << 8);
+                    ml = (t & 15u) + 4u;
+                    if (ml == 19u) ml += win[q + 2u];
+                    lit = (uint32_t)(wb + (int32_t)lit);
+                    my_tok = (uint32_t)(wb + (int32_t)x); my_nxt = (uint32_t)(wb + (int32_t)nxt);
+                }
+                const uint32_t nh = (uint32_t)__popc(__ballot_sync(FULL_MASK, have));     // `have` lanes form a run that starts at lane n
+                if (nh == 0u) break;
+                n += nh;
+                tip = __shfl_sync(FULL_MASK, my_nxt, n - 1u);
+                if (n == 32u) break;
             }
-            // lane i: the i-th token after the entry point
-            uint32_t x = ip - (uint32_t)wb;
-            if (lane & 1u) x = T1[x];
-            if (lane & 2u) x = T2[x];
-            if (lane & 4u) x = T4[x];
-            if (lane & 8u) x = T8[x];
-            if (lane & 16u) x = T16[x];
-            const uint32_t nxt = T1[x];                                     // entries 128..255 are identity: harmless for x >= 128
-            const bool have = x < 128u && nxt != WSTOP;
-            uint32_t ll = 0, ml = 0, off = 1, lit = 0;
-            if (have) {
-                const uint32_t t = win[x];
-                ll = t >> 4; lit = x + 1u;
-                if (ll == 15u) { ll += win[lit]; ++lit; }
-                const uint32_t q = lit + ll;
-                off = (uint32_t)win[q] | ((uint32_t)win[q + 1u] << 8);
-                ml = (t & 15u) + 4u;
-                if (ml == 19u) ml += win[q + 2u];
-            }
-            const uint32_t nh = (uint32_t)__popc(__ballot_sync(FULL_MASK, have));     // `have` lanes form a prefix
-            const uint32_t sz = (lane < nh) ? ll + ml : 0u;
-            uint32_t run = sz;
-            #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, run, d); if ((int)lane >= d) run += y; }
-            const uint32_t seq_op = op0 + run - sz;                         // where this lane's sequence starts
-            const bool fits = lane < nh && seq_op < o_fast;                 // again a prefix
-            n = (uint32_t)__popc(__ballot_sync(FULL_MASK, fits));
             if (n) {
-                const bool bad = lane < n && (off == 0u || off > seq_op + ll + reach);           // lz4.c:1977
+                const uint32_t sz = (lane < n) ? ll + ml : 0u;
+                uint32_t run = sz;
+                #pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, run, d); if ((int)lane >= d) run += y; }
+                const uint32_t seq_op = op0 + run - sz;                         // where this lane's sequence starts
+                const bool fits = lane < n && seq_op < o_fast;                  // a prefix (lane 0 always fits)
+                const uint32_t nf = (uint32_t)__popc(__ballot_sync(FULL_MASK, fits));
+                const bool bad = lane < nf && (off == 0u || off > seq_op + ll + reach);              // lz4.c:1977
                 if (__any_sync(FULL_MASK, bad)) { err = E_decompressionFailed; break; }
-                // entry point and output position after the n sequences taken
-                const uint32_t nx_pos = __shfl_sync(FULL_MASK, n < 32u ? x : nxt, n < 32u ? n : 31u);
-                const uint32_t nx_op = __shfl_sync(FULL_MASK, n < 32u ? seq_op : seq_op + sz, n < 32u ? n : 31u);
-                ip = (uint32_t)(wb + (int32_t)nx_pos); op = nx_op;
-                if (lane < n) { my_lit = (uint32_t)(wb + (int32_t)lit); my_ll = ll; my_ml = ml; my_off = off; }
-                my_packed = false;
+                // entry point and output position after the nf sequences taken
+                const uint32_t nx_ip = __shfl_sync(FULL_MASK, my_tok, nf & 31u);
+                const uint32_t nx_op = __shfl_sync(FULL_MASK, nf < 32u ? seq_op : seq_op + sz, nf < 32u ? nf : 31u);
+                ip = (nf < n) ? nx_ip : tip; op = nx_op;
+                n = nf;
+                my_lit = lit; my_ll = ll; my_ml = ml; my_off = off; my_op_fast = seq_op;
+                if (lane >= n) { my_ll = 0; my_ml = 0; my_off = 1; }
+                my_packed = false; fast_batch = true;
             }
         }
         if (n == 0)
@@ -437,8 +453,8 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
         if (err) break;                                                     // nothing of a bad batch is copied
         if (my_packed) { my_lit = my_a & 0x3FFFFFu; my_ll = my_a >> 22; my_off = my_b & 0xFFFFu; my_ml = my_b >> 16; }
         // output position of sequence i = op0 + sum of the sizes of the sequences before it
-        uint32_t my_op;
-        {
+        uint32_t my_op = my_op_fast;
+        if (!fast_batch) {
             const uint32_t sz = my_ll + my_ml;
             uint32_t x = sz;
             #pragma unroll
@@ -476,7 +492,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
                 } else {
                     const bool ready = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
                                        ((int)lane == f || (int64_t)my_mop + my_need <= (int64_t)W);
-                    if (ready) lane_match(dp + my_mop, my_off, my_ml);
+                    if (ready) { if (my_off >= my_ml) lane_copy(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match(dp + my_mop, my_off, my_ml); }
                     pending &= ~__ballot_sync(FULL_MASK, ready);
                 }
                 __syncwarp();
@@ -487,7 +503,10 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
     return err;
 }
 
-__global__ void __launch_bounds__(DEC_WARPS * 32)
+#ifndef B2_DEC_MINCTAS
+#define B2_DEC_MINCTAS 4      // 8 warps x 4 CTAs: 64 registers per thread, 32 warps per SM
+#endif
+__global__ void __launch_bounds__(DEC_WARPS * 32, B2_DEC_MINCTAS)
 decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint64_t dst_cap,
                      const FrameIndex* __restrict__ fi, const BlockRef* __restrict__ blocks,
                      const Piece* __restrict__ pieces, const Chain* __restrict__ chains,

@@ -6,12 +6,15 @@
 
 namespace b2 {
 
-constexpr int DEC_WARPS = 4;          // warps per CTA in the sequence decoder
+#ifndef B2_DEC_WARPS
+#define B2_DEC_WARPS 8
+#endif
+constexpr int DEC_WARPS = B2_DEC_WARPS;          // warps per CTA in the sequence decoder
 #ifndef B2_ENC_WARPS
 #define B2_ENC_WARPS 8
 #endif
 #ifndef B2_ENC_SMEM_WARPS
-#define B2_ENC_SMEM_WARPS 3
+#define B2_ENC_SMEM_WARPS 2
 #endif
 #ifndef B2_ENC_CTAS
 #define B2_ENC_CTAS 4
