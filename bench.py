@@ -27,6 +27,26 @@ sys.path.insert(0, ROOT)
 METRIC = "lz4f_roundtrip_uncompressed_GBps"
 UNIT = "GB/s"
 WORKLOAD = "config2: 1 GiB synthetic log-like stream (tools/b2gen.c, splitmix64 seed 0x10C5), 4 MB independent blocks, compress + decompress"
+# the other BASELINE.json shapes (parity-test cases; measured with --workload for profiles/, never the default line)
+WORKLOADS = {
+    "loglike": WORKLOAD,
+    "textlike": "config1 shape: text-like stream (tools/b2gen.c b2gen_textlike, datagen-style 50 % match probability), compress + decompress",
+    "zeros": "config5 shape: all-zero stream (one long overlapping match per block), compress + decompress",
+    "random": "config5 shape: incompressible random stream (every block stored), compress + decompress",
+}
+
+
+def fill(gen, ptr, n, workload, seed):
+    if workload == "loglike":
+        gen.b2gen_loglike(ptr, n, seed)
+    elif workload == "textlike":
+        gen.b2gen_textlike(ptr, n, seed)
+    elif workload == "random":
+        gen.b2gen_random(ptr, n, seed)
+    elif workload == "zeros":
+        C.memset(ptr, 0, n)
+    else:
+        raise SystemExit(f"unknown workload {workload}")
 
 
 def load_gen():
@@ -36,6 +56,9 @@ def load_gen():
     lib = C.CDLL(path)
     lib.b2gen_loglike.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
     lib.b2gen_loglike.restype = None
+    for f in (lib.b2gen_textlike, lib.b2gen_random):
+        f.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
+        f.restype = None
     return lib
 
 
@@ -193,6 +216,8 @@ def main():
     ap.add_argument("--no-index", action="store_true", help="plain frames (drop-in default) instead of seekable ones")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--workload", default="loglike", choices=sorted(WORKLOADS))
+    ap.add_argument("--block-id", type=int, default=7, help="frame block size id 4..7 = 64 KB .. 4 MB")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -214,11 +239,14 @@ def main():
     gen = load_gen()
     n = args.size_mib << 20
     index = 0 if args.no_index else 1
-    codec = pkg.Codec(local, block_size_id=7, sub_block_log2=args.sub_log2, write_index=index, use_index=1)
+    codec = pkg.Codec(local, block_size_id=args.block_id, sub_block_log2=min(args.sub_log2, 8 + 2 * args.block_id),
+                      write_index=index, use_index=1)
+    workload = WORKLOADS[args.workload]
+    block_size = 1 << (8 + 2 * args.block_id)
 
     # synthetic input: every rank its own stream (weak scaling), generated on the host, moved to HBM once
     host_in = torch.empty(n, dtype=torch.uint8).pin_memory()
-    gen.b2gen_loglike(host_in.data_ptr(), n, 0x10C5 + rank)
+    fill(gen, host_in.data_ptr(), n, args.workload, 0x10C5 + rank)
     d_in = host_in.cuda()
     cap = pkg.compress_bound(n, codec.prefs)
     d_comp = torch.empty(cap, dtype=torch.uint8, device="cuda")
@@ -324,7 +352,7 @@ def main():
     line = {"metric": METRIC, "value": world * n / (wall_ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": args.warmup, "ms_per_step": wall_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "bytes_per_gpu": n, "block_size": 4 << 20, "sub_block": 1 << args.sub_log2,
+            "config": {"workload": workload, "bytes_per_gpu": n, "block_size": block_size, "sub_block": 1 << min(args.sub_log2, 8 + 2 * args.block_id),
                        "frame": "seekable (B2IX index frame appended)" if index else "plain (drop-in default)",
                        "l2": "inputs larger than L2 (1 GiB stream vs 126 MB L2)", "parallelism": f"{world} independent streams, no collective"},
             "compress_GBps": world * n / (c_ms * 1e-3) / 1e9, "decompress_GBps": world * n / (d_ms * 1e-3) / 1e9,

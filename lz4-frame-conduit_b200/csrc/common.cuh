@@ -23,10 +23,52 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
 }
 
 // Copy n bytes with every thread of a group (nthreads threads, this one is `tid`).  dst/src may have
-// any alignment and must not overlap.  Bulk part: 4-byte stores, source re-aligned with a funnel shift,
-// so a warp writes 128 contiguous bytes per instruction.
+// any alignment and must not overlap.  Bulk part: 16-byte stores to the aligned destination; a misaligned
+// source is read as the two aligned 16-byte chunks that hold the bytes and re-aligned with funnel shifts
+// (every chunk that is read contains at least one byte of [src, src + n)).
+template <int WS>
+__device__ __forceinline__ void copy_shifted(uint4* __restrict__ d4, const uint4* __restrict__ s4, uint64_t nq,
+                                             uint32_t bs, uint32_t tid, uint32_t nthreads) {
+    #pragma unroll 2
+    for (uint64_t i = tid; i < nq; i += nthreads) {
+        const uint4 a = s4[i], b = s4[i + 1];
+        const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        uint4 o;
+        o.x = __funnelshift_r(w[WS], w[WS + 1], bs); o.y = __funnelshift_r(w[WS + 1], w[WS + 2], bs);
+        o.z = __funnelshift_r(w[WS + 2], w[WS + 3], bs); o.w = __funnelshift_r(w[WS + 3], w[WS + 4], bs);
+        d4[i] = o;
+    }
+}
 __device__ __forceinline__ void group_copy(uint8_t* dst, const uint8_t* src, uint64_t n,
                                            uint32_t tid, uint32_t nthreads) {
+    if (n < 64) { for (uint64_t i = tid; i < n; i += nthreads) dst[i] = src[i]; return; }
+    const uint32_t head = (uint32_t)((16u - ((uintptr_t)dst & 15u)) & 15u);
+    if (tid < head) dst[tid] = src[tid];
+    dst += head; src += head; n -= head;
+    const uint64_t nq = n >> 4;
+    const uint32_t sh = (uint32_t)((uintptr_t)src & 15u);
+    const uint4* s4 = (const uint4*)(src - sh);
+    uint4* d4 = (uint4*)dst;
+    if (sh == 0) {
+        #pragma unroll 4
+        for (uint64_t i = tid; i < nq; i += nthreads) d4[i] = s4[i];
+    } else {
+        const uint32_t bs = (sh & 3u) * 8u;
+        switch (sh >> 2) {
+            case 0: copy_shifted<0>(d4, s4, nq, bs, tid, nthreads); break;
+            case 1: copy_shifted<1>(d4, s4, nq, bs, tid, nthreads); break;
+            case 2: copy_shifted<2>(d4, s4, nq, bs, tid, nthreads); break;
+            default: copy_shifted<3>(d4, s4, nq, bs, tid, nthreads); break;
+        }
+    }
+    const uint64_t done = nq << 4;
+    if (tid < (uint32_t)(n - done)) dst[done + tid] = src[done + tid];
+}
+
+// Small-footprint variant for code that sits inside a hot loop (few registers): 4-byte stores, source re-aligned
+// with a funnel shift.
+__device__ __forceinline__ void group_copy_small(uint8_t* dst, const uint8_t* src, uint64_t n,
+                                                 uint32_t tid, uint32_t nthreads) {
     if (n < 64) { for (uint64_t i = tid; i < n; i += nthreads) dst[i] = src[i]; return; }
     uint32_t head = (uint32_t)((4u - ((uintptr_t)dst & 3u)) & 3u);
     if (tid < head) dst[tid] = src[tid];
@@ -35,18 +77,8 @@ __device__ __forceinline__ void group_copy(uint8_t* dst, const uint8_t* src, uin
     uint32_t sh = (uint32_t)((uintptr_t)src & 3u) * 8u;
     const uint32_t* sw = (const uint32_t*)((uintptr_t)src & ~(uintptr_t)3);
     uint32_t* dw = (uint32_t*)dst;
-    if (sh == 0) {
-        if ((((uintptr_t)dw | (uintptr_t)sw) & 15u) == 0) {
-            uint64_t nq = nw >> 2;
-            const uint4* s4 = (const uint4*)sw; uint4* d4 = (uint4*)dw;
-            for (uint64_t i = tid; i < nq; i += nthreads) d4[i] = s4[i];
-            for (uint64_t i = (nq << 2) + tid; i < nw; i += nthreads) dw[i] = sw[i];
-        } else {
-            for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = sw[i];
-        }
-    } else {
-        for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = __funnelshift_r(sw[i], sw[i + 1], sh);
-    }
+    if (sh == 0) { for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = sw[i]; }
+    else { for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = __funnelshift_r(sw[i], sw[i + 1], sh); }
     uint64_t done = nw << 2;
     if (tid < (uint32_t)(n - done)) dst[done + tid] = src[done + tid];
 }

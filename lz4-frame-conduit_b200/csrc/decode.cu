@@ -34,16 +34,18 @@ __device__ const uint8_t* find_index(const uint8_t* src, uint64_t n, uint64_t* p
 __global__ void __launch_bounds__(256)
 frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap, uint32_t mode,
                   FrameIndex* __restrict__ fi, BlockRef* __restrict__ blocks, uint32_t cap_blocks,
-                  Piece* __restrict__ pieces, uint32_t cap_pieces, Chain* __restrict__ chains)
+                  Piece* __restrict__ pieces, uint32_t cap_pieces, Chain* __restrict__ chains,
+                  uint32_t* __restrict__ stored_list)
 {
     __shared__ FrameIndex s;
+    __shared__ uint32_t s_nstored;
     __shared__ const uint8_t* s_idx;
     __shared__ uint32_t s_bad;
     const uint32_t tid = threadIdx.x;
 
     if (tid == 0) {
         s = FrameIndex{};
-        s_idx = nullptr; s_bad = 0;
+        s_idx = nullptr; s_bad = 0; s_nstored = 0;
         uint8_t hdr[HEADER_MAX];
         uint32_t hn = n < (uint64_t)HEADER_MAX ? (uint32_t)n : (uint32_t)HEADER_MAX;
         for (uint32_t i = 0; i < hn; ++i) hdr[i] = src[i];
@@ -131,7 +133,8 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
                 if (k + 1 < ncb) { tok_n = ld_le32_dev(ce + 8); out_n = ld_le32_dev(ce + 12); }
                 if ((k == 0 && (tok != 0 || out != 0)) || tok >= tok_n || out > out_n || tok_n > cs || out_n > us) { s_bad = 1; break; }
                 Piece pc; pc.src_off = a + 4 + tok; pc.src_len = tok_n - tok;
-                pc.flags = PIECE_EXACT | (br.stored ? PIECE_STORED : 0u) | (k + 1 == ncb ? PIECE_ENDS_BLOCK : 0u);
+                pc.flags = PIECE_EXACT | (br.stored ? (PIECE_STORED | PIECE_BULK) : 0u) | (k + 1 == ncb ? PIECE_ENDS_BLOCK : 0u);
+                if (br.stored) stored_list[atomicAdd(&s_nstored, 1u)] = fc + k;     // copied by copy_stored_kernel
                 pc.dst_len = out_n - out; pc.block = b; pc.dst_rel = out; pc.pad = 0;
                 pieces[fc + k] = pc;
                 Chain ch; ch.dst_off = d + out; ch.first_piece = fc + k; ch.n_pieces = 1;
@@ -142,7 +145,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
         __syncthreads();
         if (!s_bad) {
             if (tid == 0) {
-                s.indexed = 1; s.layout_known = 1;
+                s.indexed = 1; s.layout_known = 1; s.n_stored = s_nstored;
                 if (s.total_out > dst_cap) s.err = E_dstMaxSize_tooSmall;
                 if (s.desc.has_content_size && s.desc.content_size != s.total_out) s.err = E_frameSize_wrong;
                 *fi = s;
@@ -151,7 +154,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
         }
         // fall through to the serial walk with the index ignored
         __syncthreads();
-        if (tid == 0) { s.n_blocks = s.n_pieces = s.n_chains = 0; s.total_out = 0; s.consumed = s.consumed_with_index = 0; }
+        if (tid == 0) { s.n_blocks = s.n_pieces = s.n_chains = 0; s.total_out = 0; s.consumed = s.consumed_with_index = 0; s_nstored = 0; }
         __syncthreads();
     }
 
@@ -174,8 +177,11 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
                 Piece pc; pc.src_off = ip; pc.src_len = cs;
                 pc.flags = PIECE_ENDS_BLOCK | (br.stored ? PIECE_STORED : 0u);
                 pc.dst_len = 0; pc.block = nb; pc.dst_rel = 0; pc.pad = 0;
+                if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) {
+                    Chain ch; ch.dst_off = br.dst_off; ch.first_piece = nb; ch.n_pieces = 1; chains[nb] = ch;
+                    if (br.stored) { pc.flags |= PIECE_BULK; stored_list[s_nstored++] = nb; }
+                }
                 pieces[nb] = pc;
-                if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) { Chain ch; ch.dst_off = br.dst_off; ch.first_piece = nb; ch.n_pieces = 1; chains[nb] = ch; }
             }
             ++nb;
             ip += (uint64_t)cs + bc;
@@ -187,7 +193,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
         s.need_blocks = nb; s.need_pieces = nb;
         if (err == OK && (nb > cap_blocks || nb > cap_pieces)) err = E_allocation_failed;
         s.err = err;
-        s.n_blocks = nb; s.n_pieces = nb;
+        s.n_blocks = nb; s.n_pieces = nb; s.n_stored = s_nstored;
         s.consumed = ip; s.consumed_with_index = ip;
         s.total_out = (uint64_t)nb * s.block_size;                   // upper bound
         if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) { s.n_chains = nb; s.layout_known = 0; }
@@ -213,6 +219,8 @@ struct Cursor {            // what the warp knows about the piece it is decoding
     uint32_t opiece_end;   // exact end of this piece's output (PIECE_EXACT) or == oend
     uint8_t* win;          // this warp's shared memory: 272-byte window of the compressed stream + 5 link tables of 256 bytes
     const uint8_t* src_end;// end of the compressed buffer (words that start at or after it are not read)
+    uint32_t p_dst, p_off, p_ml;  // DEC_PAUSED: a huge overlapping match the caller fills (dp + p_dst, offset, length)
+    bool p_done;           // ... and whether the piece ended with it
     uint32_t reach;        // a match at output position m may reach back `m + reach` bytes (mod 2^32):
                            // independent piece: -piece_start;  linked: bytes of earlier output in front of the block
 };
@@ -244,23 +252,52 @@ __device__ __forceinline__ void lane_match(uint8_t* d, uint32_t off, uint32_t n)
 }
 
 // Warp-cooperative match copy (long matches): the source window [d - off, d) is final.
-__device__ __forceinline__ void warp_match(uint8_t* d, uint32_t offset, uint64_t ml, uint32_t lane) {
+//   off >= ml            plain copy
+//   16 % off == 0        (run-length style: 1, 2, 4, 8, 16) every aligned 16-byte chunk of the run holds the same
+//                        pattern, built once per lane in registers and streamed out with 16-byte stores
+//   other overlaps       the first bytes are replicated directly, then the valid region doubles: each round copies a
+//                        whole number of periods from what is already there (non-overlapping, so the wide copy applies)
+// (rare paths are kept out of line so that their registers do not weigh on the sequence loop)
+__device__ __forceinline__ void warp_match_overlap(uint8_t* d, uint32_t offset, uint64_t ml, uint32_t lane) {
     const uint8_t* m = d - offset;
-    if (offset >= ml) {
-        group_copy(d, m, ml, lane, 32);
-    } else if (offset >= 32) {
-        for (uint64_t i = lane; i < ml; i += 32) d[i] = m[i % offset];
-    } else {
-        // short period, long run: each lane owns byte positions i = lane + 32k; its index inside the
-        // pattern advances by 32 mod offset every step.  Bulk part as 4-byte words once 4-aligned.
-        uint32_t r = lane % offset, step = 32u % offset;
-        for (uint64_t i = lane; i < ml; i += 32) {
-            d[i] = m[r];
-            r += step; if (r >= offset) r -= offset;
+    if ((16u % offset) == 0u && ml >= 64u) {
+        const uint32_t head = (uint32_t)((16u - ((uintptr_t)d & 15u)) & 15u);
+        if (lane < head) d[lane] = m[lane % offset];
+        uint32_t pw[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t v = 0;
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) v |= (uint32_t)m[(head + 4u * j + k) % offset] << (8 * k);
+            pw[j] = v;
         }
+        __syncwarp();
+        const uint4 P = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+        uint4* d4 = (uint4*)(d + head);
+        const uint64_t nq = (ml - head) >> 4;
+        #pragma unroll 4
+        for (uint64_t q = lane; q < nq; q += 32) d4[q] = P;
+        const uint64_t done = head + (nq << 4);
+        if (lane < (uint32_t)(ml - done)) d[done + lane] = m[(done + lane) % offset];
+        return;
+    }
+    // direct replication of the first bytes (enough for the doubling rounds to use wide copies soon)
+    uint64_t done = ml < 256u ? ml : 256u;
+    {
+        uint32_t r = lane % offset; const uint32_t step = 32u % offset;
+        for (uint32_t i = lane; i < (uint32_t)done; i += 32) { d[i] = m[r]; r += step; if (r >= offset) r -= offset; }
+    }
+    while (done < ml) {
+        __syncwarp();
+        const uint64_t L = ((offset + done) / offset) * offset;         // whole periods available behind d + done
+        const uint64_t cnt = (ml - done) < L ? (ml - done) : L;
+        group_copy(d + done, d + done - L, cnt, lane, 32);
+        done += cnt;
     }
 }
 
+constexpr uint32_t DEC_PAUSED = 0xFFFFFFFEu;   // decode_piece: stopped in front of a huge overlapping match (see Cursor::p_*)
+constexpr uint32_t HUGE_MATCH = 512u;          // overlapping matches at least this long are filled outside the sequence loop
 constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
 #ifndef B2_DEC_LANE_CAP
 #define B2_DEC_LANE_CAP 32
@@ -299,7 +336,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
     uint8_t* const win = c.win;
     uint8_t* const T1 = win + 272, * const T2 = T1 + 256, * const T4 = T2 + 256, * const T8 = T4 + 256, * const T16 = T8 + 256;
     int32_t wb = 0; bool win_ok = false;                                    // window = stream bytes [wb, wb + 256)
-    bool finished = false;
+    bool finished = false, paused = false;
     while (!finished) {
         uint32_t my_a = 0, my_b = 0, my_lit = 0, my_ll = 0, my_ml = 0, my_off = 1;
         bool my_packed = true, fast_batch = false;
@@ -442,13 +479,13 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
             const uint32_t mop = op + ll;
             if (offset == 0u || offset > mop + reach) { err = E_decompressionFailed; break; }           // lz4.c:1977
             if ((uint64_t)mop + ml + 5u > oend || (uint64_t)mop + ml > opend) { err = E_decompressionFailed; break; } // lz4.c:2033-2035
-            if (lane == n) { my_lit = lit; my_ll = ll; my_ml = ml; my_off = offset; my_packed = false; }
+            const bool huge = ml >= HUGE_MATCH && offset < ml;             // run-length style: filled by the caller, out of this loop
+            if (lane == n) { my_lit = lit; my_ll = ll; my_ml = huge ? 0u : ml; my_off = offset; my_packed = false; }
             op = mop + ml;
-            if (ip == pend && !ends_block) {                                // sub-block ends after a match
-                if (op != opend) err = E_decompressionFailed;
-                ++n; finished = true;
-                break;
-            }
+            const bool piece_ends = (ip == pend && !ends_block);           // sub-block ends after a match
+            if (piece_ends && op != opend) { err = E_decompressionFailed; break; }
+            if (huge) { c.p_dst = mop; c.p_off = offset; c.p_ml = ml; c.p_done = piece_ends; paused = true; ++n; finished = true; break; }
+            if (piece_ends) { ++n; finished = true; break; }
         }
         if (err) break;                                                     // nothing of a bad batch is copied
         if (my_packed) { my_lit = my_a & 0x3FFFFFu; my_ll = my_a >> 22; my_off = my_b & 0xFFFFu; my_ml = my_b >> 16; }
@@ -471,7 +508,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
                 const int j = __ffs(longm) - 1; longm &= longm - 1;
                 const uint32_t l = __shfl_sync(FULL_MASK, my_lit, j), o = __shfl_sync(FULL_MASK, my_op, j);
                 const uint32_t len = __shfl_sync(FULL_MASK, my_ll, j);
-                group_copy(dp + o, sp + l, len, lane, 32);
+                group_copy_small(dp + o, sp + l, len, lane, 32);
             }
         }
         __syncwarp();
@@ -487,7 +524,11 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
                 const uint32_t ml_f = __shfl_sync(FULL_MASK, my_ml, f);
                 if (ml_f > LANE_CAP) {
                     const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
-                    warp_match(dp + W, off_f, ml_f, lane);
+                    if (off_f >= ml_f) group_copy_small(dp + W, dp + W - off_f, ml_f, lane, 32);
+                    else {                                                  // overlapping, < HUGE_MATCH or from the short path: period replication
+                        const uint8_t* m = dp + W - off_f; uint32_t r = lane % off_f; const uint32_t step = 32u % off_f;
+                        for (uint32_t i = lane; i < ml_f; i += 32) { dp[W + i] = m[r]; r += step; if (r >= off_f) r -= off_f; }
+                    }
                     pending &= ~(1u << f);
                 } else {
                     const bool ready = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
@@ -500,7 +541,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
         }
     }
     c.ip = ip; c.op = op;
-    return err;
+    return err ? err : (paused ? DEC_PAUSED : 0u);
 }
 
 #ifndef B2_DEC_MINCTAS
@@ -549,7 +590,7 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
             if (pc.flags & PIECE_STORED) {
                 if (op + pc.src_len > dst_cap) po.err = E_dstMaxSize_tooSmall;
                 else {
-                    group_copy(dst + op, src + pc.src_off, pc.src_len, lane, 32);
+                    if (!(pc.flags & PIECE_BULK)) group_copy_small(dst + op, src + pc.src_off, pc.src_len, lane, 32);   // bulk ones: copy_stored_kernel
                     po.out_len = pc.src_len; op += pc.src_len;
                 }
             } else {
@@ -566,7 +607,15 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
                 // linked blocks reach up to 64 KB into the earlier output of the chain (lz4frame.c:1286-1349)
                 if (linked) { uint64_t h = blk_out - chain_start + hist; cu.reach = h > 0x40000000ull ? 0x40000000u : (uint32_t)h; }
                 else cu.reach = 0u - op_rel;
-                uint32_t e = decode_piece(cu, (pc.flags & PIECE_ENDS_BLOCK) != 0);
+                uint32_t e;
+                for (;;) {
+                    e = decode_piece(cu, (pc.flags & PIECE_ENDS_BLOCK) != 0);
+                    if (e != DEC_PAUSED) break;
+                    __syncwarp();
+                    warp_match_overlap(cu.dp + cu.p_dst, cu.p_off, cu.p_ml, lane);
+                    __syncwarp();
+                    if (cu.p_done) { e = 0; break; }
+                }
                 const uint32_t produced = cu.op - op_rel;
                 if ((pc.flags & PIECE_EXACT) && e == 0 && produced != pc.dst_len) e = E_decompressionFailed;
                 if (e && ocap < block_size) e = E_dstMaxSize_tooSmall;          // ran out of destination
@@ -577,6 +626,32 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
             if (lane == 0) outs[pi] = po;
             __syncwarp();
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// stored blocks of independent-block frames (lz4frame.c:1546-1580 copies them with memcpy): plain wide copies,
+// every CTA takes 64 KB slices of the blocks the scan listed.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+copy_stored_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint64_t dst_cap,
+                   const FrameIndex* __restrict__ fi, const Piece* __restrict__ pieces,
+                   const Chain* __restrict__ chains, const uint32_t* __restrict__ stored_list)
+{
+    if (fi->err != OK) return;
+    const uint32_t ns = fi->n_stored;
+    if (ns == 0) return;
+    constexpr uint32_t SLICE = 65536u;
+    const uint32_t per = (fi->block_size + SLICE - 1u) / SLICE;
+    const uint64_t total = (uint64_t)ns * per;
+    for (uint64_t it = blockIdx.x; it < total; it += gridDim.x) {
+        const uint32_t k = (uint32_t)(it / per), sl = (uint32_t)(it - (uint64_t)k * per);
+        const Chain ch = chains[stored_list[k]];
+        const Piece pc = pieces[ch.first_piece];
+        const uint32_t off = sl * SLICE;
+        if (off >= pc.src_len || ch.dst_off + pc.src_len > dst_cap) continue;
+        const uint32_t len = pc.src_len - off < SLICE ? pc.src_len - off : SLICE;
+        group_copy(dst + ch.dst_off + off, src + pc.src_off + off, len, threadIdx.x, blockDim.x);
     }
 }
 

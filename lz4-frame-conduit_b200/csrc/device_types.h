@@ -18,7 +18,8 @@ struct BlockRef {
 
 // A piece = a run of whole LZ4 sequences decoded in order by one warp.
 //   foreign frame: piece = block;   indexed frame (ours): piece = independent sub-block of a block.
-enum : uint32_t { PIECE_STORED = 1u, PIECE_ENDS_BLOCK = 2u, PIECE_EXACT = 4u };
+enum : uint32_t { PIECE_STORED = 1u, PIECE_ENDS_BLOCK = 2u, PIECE_EXACT = 4u,
+                  PIECE_BULK = 8u };   // stored block whose copy is done by copy_stored_kernel, not by the decoding warp
 struct Piece {
     uint64_t src_off;     // first token of the piece (absolute offset in the compressed buffer)
     uint32_t src_len;     // compressed bytes of the piece
@@ -57,6 +58,8 @@ struct FrameIndex {
     uint64_t total_out;       // decoded size when known up front (indexed), else upper bound n_blocks*block_size
     uint32_t need_blocks;     // table sizes the scan wanted (for the retry after E_allocation_failed)
     uint32_t need_pieces;
+    uint32_t n_stored;        // stored blocks listed for copy_stored_kernel
+    uint32_t pad0;
     FrameDesc desc;
 };
 

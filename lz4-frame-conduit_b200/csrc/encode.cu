@@ -159,7 +159,9 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
         Pending pd = {0, 0, 0, 0};
 
         while (T0 < limit) {
-            const uint32_t sl = miss < 3u ? miss : 3u;                        // probe stride 1, 2, 4, 8
+            // probe stride 1, 2, 4, 8 after 0..3 steps without a hit, 16 after 8, 32 after 16 (the reference's skip
+            // acceleration grows the same way: one more byte per 64 failed attempts, lz4.c:895-905)
+            const uint32_t sl = miss < 3u ? miss : miss < 8u ? 3u : miss < 16u ? 4u : 5u;
             const uint32_t span = 128u << sl;
             if (lane < 2u && T0 + span + 128u * (lane + 1u) <= usize) prefetch_l1(base + T0 + span + 128u * lane);   // next step's input
             // ---- 1. probe
@@ -301,19 +303,39 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                         const uint32_t lp = __shfl_sync(FULL_MASK, pos, npend - 1u);
                         const uint32_t lc = b0 + (__shfl_sync(FULL_MASK, pkv, npend - 1u) & 0x3FFFFFu);
                         uint32_t len = ENC_PREMEASURE;
-                        for (;;) {
-                            const uint32_t qq = lp + len + lane * 4u;
-                            const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
-                            uint32_t nbytes = 0;
-                            if (avail) {
-                                const uint32_t xx = ld32u(base + qq) ^ ld32u(base + lc + len + lane * 4u);
-                                nbytes = xx ? (uint32_t)(__ffs(xx) - 1) >> 3 : 4u;
-                                if (nbytes > avail) nbytes = avail;
+                        for (uint32_t round = 0;; ++round) {
+                            uint32_t nbytes = 0, per;
+                            if (round == 0) {                                 // most long matches end within 128 more bytes
+                                per = 4u;
+                                const uint32_t qq = lp + len + lane * 4u;
+                                const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
+                                if (avail) {
+                                    const uint32_t xx = ld32u(base + qq) ^ ld32u(base + lc + len + lane * 4u);
+                                    nbytes = xx ? (uint32_t)(__ffs(xx) - 1) >> 3 : 4u;
+                                    if (nbytes > avail) nbytes = avail;
+                                }
+                            } else {                                          // runs: 16 bytes per lane, 512 per round
+                                per = 16u;
+                                const uint32_t qq = lp + len + lane * 16u;
+                                const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
+                                if (avail) {
+                                    const uint8_t* pa = base + qq;
+                                    const uint8_t* pb = base + lc + len + lane * 16u;
+                                    nbytes = 16u;
+                                    #pragma unroll
+                                    for (int j = 3; j >= 0; --j) {
+                                        if (4u * j < avail) {
+                                            const uint32_t xx = ld32u(pa + 4 * j) ^ ld32u(pb + 4 * j);
+                                            if (xx) nbytes = 4u * j + ((uint32_t)(__ffs(xx) - 1) >> 3);
+                                        }
+                                    }
+                                    if (nbytes > avail) nbytes = avail;
+                                }
                             }
-                            const uint32_t part = __ballot_sync(FULL_MASK, nbytes != 4u);
-                            if (part == 0) { len += 128u; continue; }
+                            const uint32_t part = __ballot_sync(FULL_MASK, nbytes != per);
+                            if (part == 0) { len += 32u * per; continue; }
                             const int g = __ffs(part) - 1;
-                            len += (uint32_t)g * 4u + __shfl_sync(FULL_MASK, nbytes, g);
+                            len += (uint32_t)g * per + __shfl_sync(FULL_MASK, nbytes, g);
                             break;
                         }
                         if (lane == npend - 1u) { fl = len; mend = pos + len; }

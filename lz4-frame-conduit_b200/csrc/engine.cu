@@ -63,7 +63,7 @@ struct b2lz4_ctx {
     cudaEvent_t ev_in = nullptr, ev_sum = nullptr;
     Small* d_small = nullptr;
     Small* h_small = nullptr;                     // pinned
-    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stage_in, stage_out, enc_tabs, ring, idx_frag, stage_in2, stage_out2;
+    DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stored, stage_in, stage_out, enc_tabs, ring, idx_frag, stage_in2, stage_out2;
     size_t ring_pos = 0; uint32_t ring_hist = 0;     // streaming linked-block decode: next output offset / valid history bytes
     b2lz4_stats stats{};
     char cuda_err[256] = {0};
@@ -207,7 +207,7 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->st) cudaStreamSynchronize(ctx->st);
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
-                       &ctx->chains, &ctx->outs, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2 }) b->release();
+                       &ctx->chains, &ctx->outs, &ctx->stored, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2 }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
@@ -355,18 +355,21 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
     CU(ctx->pieces.ensure((size_t)cap_tables * sizeof(Piece)));
     CU(ctx->chains.ensure((size_t)cap_tables * sizeof(Chain)));
     CU(ctx->outs.ensure((size_t)cap_tables * sizeof(PieceOut)));
+    CU(ctx->stored.ensure((size_t)cap_tables * sizeof(uint32_t)));
     Small* ds = ctx->d_small;
     uint32_t launches = 0;
     CU(cudaMemsetAsync(&ds->crc_bad, 0xFF, sizeof(uint32_t), ctx->st));
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
     frame_scan_kernel<<<1, 256, 0, ctx->st>>>(d_src, n, cap, mode, &ds->fi, (BlockRef*)ctx->blocks.p, cap_tables,
-                                              (Piece*)ctx->pieces.p, cap_tables, (Chain*)ctx->chains.p);
+                                              (Piece*)ctx->pieces.p, cap_tables, (Chain*)ctx->chains.p, (uint32_t*)ctx->stored.p);
     verify_block_checksums_kernel<<<std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st>>>(
         d_src, &ds->fi, (const BlockRef*)ctx->blocks.p, &ds->crc_bad);
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
     decode_chains_kernel<<<ctx->sm_count * (64 / DEC_WARPS), DEC_WARPS * 32, 0, ctx->st>>>(
         d_src, d_dst, cap, &ds->fi, (const BlockRef*)ctx->blocks.p, (const Piece*)ctx->pieces.p,
         (const Chain*)ctx->chains.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec, hist);
+    copy_stored_kernel<<<ctx->sm_count * 8, 256, 0, ctx->st>>>(d_src, d_dst, cap, &ds->fi, (const Piece*)ctx->pieces.p,
+                                                             (const Chain*)ctx->chains.p, (const uint32_t*)ctx->stored.p);
     CU(cudaEventRecord(ctx->ev[2], ctx->st));
     decode_finalize_kernel<<<1, 256, 0, ctx->st>>>(&ds->fi, (const Piece*)ctx->pieces.p, (const PieceOut*)ctx->outs.p,
                                                    &ds->crc_bad, &ds->dres, &ds->ticket_dec);
@@ -378,7 +381,7 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
         content_check_kernel<<<1, 32, 0, ctx->st>>>(&ds->fi, &ds->xxh, &ds->dres);
         launches += 3;
     }
-    launches += 4;
+    launches += 5;
     CU(cudaEventRecord(ctx->ev[3], ctx->st));
     CU(cudaMemcpyAsync(&ctx->h_small->fi, &ds->fi, sizeof(FrameIndex) + sizeof(DecodeResult), cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaGetLastError());

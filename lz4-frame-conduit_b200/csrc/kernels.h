@@ -31,7 +31,9 @@ enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u }
 // ---- decode
 __global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_cap, uint32_t mode,
                                   FrameIndex* fi, BlockRef* blocks, uint32_t cap_blocks,
-                                  Piece* pieces, uint32_t cap_pieces, Chain* chains);
+                                  Piece* pieces, uint32_t cap_pieces, Chain* chains, uint32_t* stored_list);
+__global__ void copy_stored_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap, const FrameIndex* fi,
+                                   const Piece* pieces, const Chain* chains, const uint32_t* stored_list);
 __global__ void decode_chains_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap,
                                      const FrameIndex* fi, const BlockRef* blocks, const Piece* pieces,
                                      const Chain* chains, PieceOut* outs, uint32_t* ticket, uint32_t hist);
