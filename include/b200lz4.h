@@ -95,6 +95,8 @@ void   b2lz4_pinned_free(void* p);
  * (they are what the LZ4F_* layer in lz4frame.h is built on).  Replaces the LZ4F_compressUpdate /
  * LZ4F_compressEnd / LZ4F_decompress inner loops (lz4frame.c:823-925, 984-1018, 1371-1840) with one call
  * per batch.  Prefs of the context decide block size / checksums. */
+#define B2LZ4_LEGACY_BLOCK_ID 8u /* b2lz4_frame_info.block_size_id for the [u32 size][block] units of a legacy frame
+                                   (magic 0x184C2102, 8 MB blocks, lz4/programs/lz4io.c:895-940): b2lz4_decompress_blocks_host only */
 #define B2LZ4_STREAM_FIRST 1u   /* first batch of a frame: resets the running content checksum and the decode history */
 /* n bytes -> [u32 size|stored][data][block checksum]... ; n must be a multiple of the block size except in the last batch */
 size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, unsigned flags);

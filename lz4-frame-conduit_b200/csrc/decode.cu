@@ -51,7 +51,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
         for (uint32_t i = 0; i < hn; ++i) hdr[i] = src[i];
         s.err = header_parse(hdr, hn, s.desc);
         if (s.err == OK) {
-            s.block_size = block_size_of(s.desc.block_size_id);
+            s.block_size = (mode & SCAN_LEGACY) ? LEGACY_BLOCK : block_size_of(s.desc.block_size_id);
             if (mode & SCAN_USE_INDEX) {
                 uint64_t pb = 0;
                 const uint8_t* ix = find_index(src, n, &pb);
@@ -168,6 +168,9 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
             uint32_t w = ld_le32_dev(src + ip); ip += 4;
             uint32_t cs = w & 0x7FFFFFFFu;
             if (cs == 0) break;                                      // EndMark
+            if (mode & SCAN_LEGACY) {                                // no stored flag; a block may be as large as LZ4_compressBound(8 MB)
+                if ((w >> 31) || cs > LEGACY_BLOCK + LEGACY_BLOCK / 255u + 16u) { err = E_maxBlockSize_invalid; break; }
+            } else
             if (cs > s.block_size) { err = E_maxBlockSize_invalid; break; }
             if (n - ip < (uint64_t)cs + bc) { err = E_noEndMark; break; }
             if (nb < cap_blocks && nb < cap_pieces) {

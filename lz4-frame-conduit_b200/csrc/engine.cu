@@ -848,7 +848,8 @@ static size_t ring_reserve(b2lz4_ctx* ctx, size_t cap) {
 size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info, const void* src, size_t n,
                                     void* dst, size_t cap, unsigned flags) {
     if (!ctx || !info || (!src && n) || (!dst && cap)) return err_code(E_GENERIC);
-    if (info->block_size_id < 4 || info->block_size_id > 7) return err_code(E_maxBlockSize_invalid);
+    const bool legacy = info->block_size_id == B2LZ4_LEGACY_BLOCK_ID;      // [u32 size][LZ4 block] units of a legacy frame
+    if (!legacy && (info->block_size_id < 4 || info->block_size_id > 7)) return err_code(E_maxBlockSize_invalid);
     size_t r = set_device(ctx); if (r) return r;
     Small* ds = ctx->d_small;
     if (flags & B2LZ4_STREAM_FIRST) {
@@ -858,8 +859,8 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     if (n == 0) { CU(cudaStreamSynchronize(ctx->st)); return 0; }
     // a frame of its own around the batch: header without optional fields, the blocks, an EndMark
     FrameDesc d{};
-    d.block_size_id = info->block_size_id; d.block_independent = info->block_independent ? 1u : 0u;
-    d.block_checksum = info->block_checksum ? 1u : 0u;
+    d.block_size_id = legacy ? 7u : info->block_size_id; d.block_independent = (legacy || info->block_independent) ? 1u : 0u;
+    d.block_checksum = (!legacy && info->block_checksum) ? 1u : 0u;
     uint8_t hdr[HEADER_MAX];
     const uint32_t hs = header_write(hdr, d);
     const uint32_t zero = 0;
@@ -870,7 +871,7 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     CU(cudaMemcpyAsync(din + hs + n, &zero, 4, cudaMemcpyHostToDevice, ctx->st));
     uint8_t* dout;
     uint32_t hist = 0;
-    const bool linked = !info->block_independent;
+    const bool linked = !legacy && !info->block_independent;
     if (linked) {
         r = ring_reserve(ctx, cap); if (r) return r;
         dout = (uint8_t*)ctx->ring.p + ctx->ring_pos; hist = ctx->ring_hist;
@@ -881,7 +882,7 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     const uint32_t keep_index = ctx->prefs.use_index;
     ctx->prefs.use_index = 0;                                       // a batch never carries an index frame
     size_t consumed = 0;
-    r = decompress_device_impl(ctx, din, hs + n + 4, dout, cap, &consumed, hist, SCAN_BATCH);
+    r = decompress_device_impl(ctx, din, hs + n + 4, dout, cap, &consumed, hist, SCAN_BATCH | (legacy ? SCAN_LEGACY : 0u));
     ctx->prefs.use_index = keep_index;
     if (b2lz4_is_error(r)) return r;
     if (consumed != hs + n + 4) return err_code(E_decompressionFailed);   // an EndMark inside the batch: not whole blocks

@@ -200,3 +200,18 @@ def test_lz4f_compress_fails_loudly_without_gpu(replay, pkg):
     out = C.create_string_buffer(64 << 20)
     r = replay.ref_conduit_compress(b"hello" * 100, 500, out, len(out), 0, 0)
     assert pkg.load().b2lz4_error_name(r) == b"ERROR_cudaFailure"
+
+
+def test_cli_builds_and_fails_loudly_without_gpu(pkg):
+    """b200lz4c (the haskell-lz4c twin) has no CPU codec either: without a device it must exit non-zero with the
+    reference's error text shape (Conduit.hsc:145-160)."""
+    import subprocess
+    from conftest import _have_gpu
+    cli = os.path.join(ROOT, "lz4-frame-conduit_b200", "b200lz4c")
+    if not os.path.exists(cli):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "lz4-frame-conduit_b200", "csrc")], check=True, capture_output=True)
+    assert b"Compress or decompress .lz4 files" in subprocess.run([cli, "--help"], capture_output=True).stdout   # app/Main.hs:40
+    if _have_gpu():
+        return
+    p = subprocess.run([cli], input=b"hello", capture_output=True)
+    assert p.returncode != 0 and p.stdout == b"" and b"lz4frame error: ERROR_cudaFailure" in p.stderr
