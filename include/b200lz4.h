@@ -71,6 +71,11 @@ size_t b2lz4_create(b2lz4_ctx** out, int device, const b2lz4_prefs* prefs /* NUL
 size_t b2lz4_destroy(b2lz4_ctx* ctx);                       /* NULL is a no-op */
 size_t b2lz4_set_prefs(b2lz4_ctx* ctx, const b2lz4_prefs* prefs);
 void   b2lz4_default_prefs(b2lz4_prefs* prefs);
+/* Multi-GPU host-buffer calls: b2lz4_compress_host / b2lz4_decompress_host cut the frame into chunks of
+ * whole blocks and send them round robin to lanes on these devices (each with its own streams and PCIe link); the host
+ * reassembles the output in block order.  No collective is involved — independent blocks have no exchange step.
+ * n = 0 returns to the context's own device.  The frame bytes do not depend on the device list. */
+size_t b2lz4_set_devices(b2lz4_ctx* ctx, const int* devices, int n);
 int    b2lz4_device_count(void);
 
 /* ---- sizes (replaces LZ4F_compressBound / LZ4F_compressFrameBound, lz4frame.c:324-349, 370-381) */

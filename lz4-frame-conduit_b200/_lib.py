@@ -41,6 +41,7 @@ SYMBOLS = {
     "b2lz4_create": (_sz, [C.POINTER(_vp), C.c_int, C.POINTER(Prefs)]),
     "b2lz4_destroy": (_sz, [_vp]),
     "b2lz4_set_prefs": (_sz, [_vp, C.POINTER(Prefs)]),
+    "b2lz4_set_devices": (_sz, [_vp, C.POINTER(C.c_int), C.c_int]),
     "b2lz4_default_prefs": (None, [C.POINTER(Prefs)]),
     "b2lz4_device_count": (C.c_int, []),
     "b2lz4_compress_bound": (_sz, [_sz, C.POINTER(Prefs)]),

@@ -97,6 +97,11 @@ class Codec:
             setattr(self.prefs, k, int(v))
         _check(self.lib, self.lib.b2lz4_set_prefs(self.h, C.byref(self.prefs)))
 
+    def set_devices(self, devices):
+        """Host-buffer calls shard their blocks over these CUDA devices (b2lz4_set_devices); [] = own device only."""
+        arr = (C.c_int * max(1, len(devices)))(*devices)
+        _check(self.lib, self.lib.b2lz4_set_devices(self.h, arr, len(devices)))
+
     def _ck(self, r):
         if self.lib.b2lz4_is_error(r):
             name = self.lib.b2lz4_error_name(r).decode()

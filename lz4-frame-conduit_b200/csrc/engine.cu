@@ -70,8 +70,16 @@ struct b2lz4_ctx {
     int sm_count = 148;
     // host-buffer calls cut the stream into chunks and keep several in flight, each on a lane = a child context with
     // its own stream and workspaces, so that H2D copies, kernels and D2H copies of different chunks overlap
-    b2lz4_ctx* lanes[8] = {};
+    b2lz4_ctx* lanes[32] = {};
     int n_lanes = 0;
+    // multi-GPU host-buffer calls (b2lz4_set_devices): lane k lives on devs[k % n_devs]; chunks of whole blocks go to the
+    // lanes round robin, so the blocks of one frame shard across the GPUs by block index and are reassembled in order on
+    // the host.  No collective: blocks are independent.  The running content checksum then lives in pinned host memory
+    // (every device reads and writes it in stream order).
+    int devs[16] = {};
+    int n_devs = 0;
+    XxhState* h_xxh = nullptr;
+    bool sum_host = false;                        // the running content checksum of the current frame lives in h_xxh
     uint8_t* h_frag = nullptr; size_t h_frag_cap = 0;   // pinned: index fragments of the chunks
 };
 
@@ -211,6 +219,7 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
+    if (ctx->h_xxh) cudaFreeHost(ctx->h_xxh);
     for (auto& v : ctx->ev) if (v) cudaEventDestroy(v);
     if (ctx->ev_in) cudaEventDestroy(ctx->ev_in);
     if (ctx->ev_sum) cudaEventDestroy(ctx->ev_sum);
@@ -225,6 +234,19 @@ size_t b2lz4_set_prefs(b2lz4_ctx* ctx, const b2lz4_prefs* prefs) {
     if (!ctx || !prefs) return err_code(E_GENERIC);
     if (!prefs_valid(*prefs)) return err_code(E_maxBlockSize_invalid);
     ctx->prefs = *prefs;
+    return 0;
+}
+
+size_t b2lz4_set_devices(b2lz4_ctx* ctx, const int* devices, int n) {
+    if (!ctx || n < 0 || n > 16 || (n && !devices)) return err_code(E_GENERIC);
+    int have = 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess) { cudaGetLastError(); return err_code(E_cudaFailure); }
+    for (int i = 0; i < n; ++i) if (devices[i] < 0 || devices[i] >= have) return err_code(E_GENERIC);
+    for (auto& l : ctx->lanes) { b2lz4_destroy(l); l = nullptr; }    // lanes are re-created on their new devices
+    ctx->n_lanes = 0;
+    for (int i = 0; i < n; ++i) ctx->devs[i] = devices[i];
+    ctx->n_devs = n;
+    cudaSetDevice(ctx->device);
     return 0;
 }
 
@@ -453,22 +475,64 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
 // -------------------------------------------------------------------------------------- host buffers
 // pipeline shape of the host-buffer calls: B2LZ4_LANES chunks in flight (default 4), B2LZ4_PIPE_MB per chunk (default: an
 // eighth of the stream, 32..256 MiB)
-static int pipe_lanes() { const char* e = getenv("B2LZ4_LANES"); int v = e ? atoi(e) : 4; return std::min(8, std::max(1, v)); }
-static size_t pipe_chunk(size_t n, size_t block_size) {
+static int pipe_lanes(const b2lz4_ctx* ctx) {
+    const char* e = getenv("B2LZ4_LANES"); int v = e ? atoi(e) : 4;
+    if (ctx->n_devs > 1 && !e) v = std::max(v, 2 * ctx->n_devs);      // at least two chunks in flight per GPU
+    return std::min(32, std::max(1, v));
+}
+static size_t pipe_chunk(const b2lz4_ctx* ctx, size_t n, size_t block_size) {
     const char* e = getenv("B2LZ4_PIPE_MB");
-    size_t c = e ? (size_t)std::max(1, atoi(e)) << 20 : std::min<size_t>(256u << 20, std::max<size_t>(32u << 20, n / 8));
+    const size_t parts = std::max(8, 2 * ctx->n_devs);
+    size_t c = e ? (size_t)std::max(1, atoi(e)) << 20 : std::min<size_t>(256u << 20, std::max<size_t>(32u << 20, n / parts));
     c = std::max(block_size, c / block_size * block_size);
     return c;
 }
+static bool multi_dev(const b2lz4_ctx* ctx) { return ctx->n_devs > 1; }
+static int lane_device(const b2lz4_ctx* ctx, int k) { return ctx->n_devs > 0 ? ctx->devs[k % ctx->n_devs] : ctx->device; }
 static size_t ensure_lanes(b2lz4_ctx* ctx, int want) {
     for (int k = ctx->n_lanes; k < want; ++k) {
-        size_t r = b2lz4_create(&ctx->lanes[k], ctx->device, &ctx->prefs);
+        size_t r = b2lz4_create(&ctx->lanes[k], lane_device(ctx, k), &ctx->prefs);
         if (b2lz4_is_error(r)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "lane context creation failed"); return r; }
         ctx->n_lanes = k + 1;
     }
     for (int k = 0; k < ctx->n_lanes; ++k) ctx->lanes[k]->prefs = ctx->prefs;
+    if (multi_dev(ctx) && !ctx->h_xxh) {
+        cudaError_t e = cudaHostAlloc((void**)&ctx->h_xxh, sizeof(XxhState), cudaHostAllocPortable | cudaHostAllocMapped);
+        if (e != cudaSuccess) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "cudaHostAlloc: %s", cudaGetErrorString(e)); cudaGetLastError(); return err_code(E_cudaFailure); }
+    }
+    cudaSetDevice(ctx->device);
     return 0;
 }
+// running content checksum of a host-buffer call: on one device it runs on the parent's second stream (stream order =
+// chunk order); across devices it hops from lane to lane through events, the state kept in pinned host memory
+struct SumChain {
+    b2lz4_ctx* ctx; cudaEvent_t prev = nullptr; uint32_t launches = 0;
+    void reset() {
+        ctx->sum_host = multi_dev(ctx);
+        if (ctx->sum_host) {
+            XxhState z{}; z.v[0] = XP1 + XP2; z.v[1] = XP2; z.v[2] = 0; z.v[3] = 0u - XP1;    // xxhash.c:437-449
+            *ctx->h_xxh = z;
+        } else { cudaSetDevice(ctx->device); xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ctx->d_small->xxh); ++launches; }
+    }
+    // hashes p[0, len) (device memory of lane `ln`) after `after` (an event on the lane's stream, or null); records ln->ev_sum
+    cudaError_t update(b2lz4_ctx* ln, const uint8_t* p, size_t len, cudaEvent_t after) {
+        cudaError_t e;
+        if (ctx->sum_host) {
+            if ((e = cudaSetDevice(ln->device)) != cudaSuccess) return e;
+            if (after && (e = cudaStreamWaitEvent(ln->st2, after, 0)) != cudaSuccess) return e;
+            if (prev && (e = cudaStreamWaitEvent(ln->st2, prev, 0)) != cudaSuccess) return e;
+            xxh32_stream_kernel<<<1, 256, 0, ln->st2>>>(p, len, nullptr, nullptr, ctx->h_xxh);
+            if ((e = cudaEventRecord(ln->ev_sum, ln->st2)) != cudaSuccess) return e;
+            prev = ln->ev_sum;
+        } else {
+            if (after && (e = cudaStreamWaitEvent(ctx->st2, after, 0)) != cudaSuccess) return e;
+            xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>(p, len, nullptr, nullptr, &ctx->d_small->xxh);
+            if ((e = cudaEventRecord(ln->ev_sum, ctx->st2)) != cudaSuccess) return e;
+        }
+        ++launches;
+        return cudaSuccess;
+    }
+};
 #define LANE_CU(L, call)                                                                           \
     do { cudaError_t e_ = (call);                                                                  \
          if (e_ != cudaSuccess) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s: %s (%s:%d)", #call, \
@@ -478,22 +542,31 @@ static size_t ensure_lanes(b2lz4_ctx* ctx, int want) {
 // One frame from a host buffer.  The stream is cut into chunks of whole blocks; chunk i goes to lane i mod L:
 // H2D copy -> match finder / layout / gather on the lane's stream, no host wait; chunks are completed in order
 // (their compressed size decides where the next one lands in dst) and copied back while later chunks still run.
+// mode: HOSTC_FRAME = a whole frame (header, blocks, EndMark, checksum, index); HOSTC_BLOCKS(_FIRST) = only the blocks of
+// one batch of a streamed frame (b2lz4_compress_blocks_host), the running content checksum continuing across calls
+enum : unsigned { HOSTC_FRAME = 0u, HOSTC_BLOCKS = 1u, HOSTC_BLOCKS_FIRST = 2u };
+static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, unsigned hmode);
 size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap) {
+    return compress_host_impl(ctx, src, n, dst, cap, HOSTC_FRAME);
+}
+static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void* dst, size_t cap, unsigned hmode) {
     if (!ctx || (!src && n) || !dst) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
     ctx->stats = b2lz4_stats{};
-    const b2lz4_prefs pr = ctx->prefs;
+    const bool whole = hmode == HOSTC_FRAME;
+    b2lz4_prefs pr = ctx->prefs;
+    if (!whole) pr.write_index = 0;
     const size_t bs = block_size_of(pr.block_size_id ? pr.block_size_id : 7u);
-    const size_t chunk = pipe_chunk(n, bs);
+    const size_t chunk = pipe_chunk(ctx, n, bs);
     const size_t nchunks = n ? (n + chunk - 1) / chunk : 0;
-    const int L = (int)std::min<size_t>((size_t)pipe_lanes(), std::max<size_t>(1, nchunks));
+    const int L = (int)std::min<size_t>((size_t)pipe_lanes(ctx), std::max<size_t>(1, nchunks));
     r = ensure_lanes(ctx, L); if (r) return r;
     uint8_t* out = (uint8_t*)dst;
-    size_t o = b2lz4_frame_header_write(out, cap, &pr, n);
+    size_t o = whole ? b2lz4_frame_header_write(out, cap, &pr, n) : 0;
     if (b2lz4_is_error(o)) return o;
     const bool sum = pr.content_checksum != 0, want_index = pr.write_index != 0;
-    Small* ds = ctx->d_small;
-    if (sum) xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh);
+    SumChain sc{ctx};
+    if (sum && hmode != HOSTC_BLOCKS) sc.reset();
     std::vector<uint8_t> ix_blocks, ix_chains;             // index entries gathered from the chunks
     struct Frag { size_t off; uint32_t nb, nc, chain_base; };
     std::vector<Frag> frags;
@@ -508,7 +581,7 @@ size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst,
             ctx->h_frag_cap = need + need / 4;
         }
     }
-    uint32_t chains_total = 0, blocks_total = 0, launches = sum ? 1u : 0u;
+    uint32_t chains_total = 0, blocks_total = 0, launches = 0;
     float ms_main = 0, ms_total = 0;
     cudaEvent_t t0 = ctx->ev[4], t1 = ctx->ev[5];
     CU(cudaEventRecord(t0, ctx->st));
@@ -516,17 +589,15 @@ size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst,
     auto submit = [&](size_t i) -> size_t {
         b2lz4_ctx* ln = ctx->lanes[i % L];
         const size_t off = i * chunk, len = std::min(chunk, n - off);
-        LANE_CU(ln, cudaSetDevice(ctx->device));
+        LANE_CU(ln, cudaSetDevice(ln->device));
         LANE_CU(ln, ln->stage_in.ensure(len + 16));
         LANE_CU(ln, ln->stage_out.ensure(b2lz4_compress_bound(len, &pr) + 16));
         if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // the checksum pass of the lane's previous chunk
         LANE_CU(ln, cudaMemcpyAsync(ln->stage_in.p, (const uint8_t*)src + off, len, cudaMemcpyHostToDevice, ln->st));
-        if (sum) {                                                              // serial XXH32 in stream order on the parent's 2nd stream
+        if (sum) {                                                              // serial XXH32 in chunk order
             LANE_CU(ln, cudaEventRecord(ln->ev_in, ln->st));
-            LANE_CU(ln, cudaStreamWaitEvent(ctx->st2, ln->ev_in, 0));
-            xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>((const uint8_t*)ln->stage_in.p, len, nullptr, nullptr, &ds->xxh);
-            LANE_CU(ln, cudaEventRecord(ln->ev_sum, ctx->st2));
-            ++launches;
+            LANE_CU(ln, sc.update(ln, (const uint8_t*)ln->stage_in.p, len, ln->ev_in));
+            LANE_CU(ln, cudaSetDevice(ln->device));
         }
         ln->stats = b2lz4_stats{};
         size_t e = compress_launch(ln, (const uint8_t*)ln->stage_in.p, len, (uint8_t*)ln->stage_out.p, ln->stage_out.cap,
@@ -537,6 +608,7 @@ size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst,
     auto complete = [&](size_t i) -> size_t {
         b2lz4_ctx* ln = ctx->lanes[i % L];
         const size_t off = i * chunk, len = std::min(chunk, n - off);
+        LANE_CU(ln, cudaSetDevice(ln->device));
         size_t c = compress_finish(ln, len);                                    // waits for the lane
         if (b2lz4_is_error(c)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return c; }
         if (o + c + 8 > cap) return err_code(E_dstMaxSize_tooSmall);
@@ -560,6 +632,15 @@ size_t b2lz4_compress_host(b2lz4_ctx* ctx, const void* src, size_t n, void* dst,
     }
     for (size_t i = nchunks > (size_t)L ? nchunks - L : 0; i < nchunks; ++i) { r = complete(i); if (r) return r; }
     for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st));
+    launches += sc.launches;
+    if (sum && multi_dev(ctx)) for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st2));
+    CU(cudaSetDevice(ctx->device));
+    if (!whole) {
+        if (sum) CU(cudaStreamSynchronize(ctx->st2));
+        ctx->stats.n_blocks = blocks_total; ctx->stats.n_chains = chains_total; ctx->stats.kernel_launches = launches;
+        ctx->stats.ms_main = ms_main; ctx->stats.ms_total = ms_total; ctx->stats.bytes_in = n; ctx->stats.bytes_out = o;
+        return o;
+    }
 
     // EndMark, content checksum, index frame: a few bytes, written by the host (lz4frame.c:998-1007)
     if (o + 4 + (sum ? 4u : 0u) > cap) return err_code(E_dstMaxSize_tooSmall);
@@ -664,6 +745,8 @@ static bool host_scan(const uint8_t* src, size_t n, bool use_index, HostFrame& f
     return true;
 }
 
+static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const HostFrame& f, size_t per_group,
+                                     void* dst, size_t cap, unsigned hmode);
 // One frame from a host buffer.  Independent-block frames are cut into groups of whole blocks on the host (a serial walk
 // over the 4-byte header words); group g goes to lane g mod L as a small frame of its own — header, the blocks, an EndMark
 // and the group's slice of the index — so that its H2D copy, decode and D2H copy overlap with the other lanes'.
@@ -674,17 +757,25 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* d
     const uint8_t* src = (const uint8_t*)src_;
     HostFrame f;
     const bool ok = n >= (size_t)HEADER_MIN && host_scan(src, n, ctx->prefs.use_index != 0, f);
-    const size_t per_group = ok && f.block_size ? std::max<size_t>(1, pipe_chunk((size_t)f.blocks.size() * f.block_size, f.block_size) / f.block_size) : 0;
+    const size_t per_group = ok && f.block_size ? std::max<size_t>(1, pipe_chunk(ctx, (size_t)f.blocks.size() * f.block_size, f.block_size) / f.block_size) : 0;
     if (!ok || !f.desc.block_independent || f.blocks.size() <= per_group)
         return decompress_host_whole(ctx, src_, n, dst, cap, consumed);           // linked frames, small frames, anything odd
+    r = decompress_host_groups(ctx, src, f, per_group, dst, cap, HOSTC_FRAME);
+    if (!b2lz4_is_error(r) && consumed) *consumed = f.consumed;
+    return r;
+}
+static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const HostFrame& f, size_t per_group,
+                                     void* dst, size_t cap, unsigned hmode) {
+    size_t r = 0;
+    const bool whole = hmode == HOSTC_FRAME;
     ctx->stats = b2lz4_stats{};
     const size_t nb = f.blocks.size(), ngroups = (nb + per_group - 1) / per_group;
-    const int L = (int)std::min<size_t>((size_t)pipe_lanes(), ngroups);
+    const int L = (int)std::min<size_t>((size_t)pipe_lanes(ctx), ngroups);
     r = ensure_lanes(ctx, L); if (r) return r;
     const uint32_t bc = f.desc.block_checksum ? 4u : 0u;
     const bool sum = f.desc.content_checksum != 0;
-    Small* ds = ctx->d_small;
-    if (sum) xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh);
+    SumChain sc{ctx};
+    if (sum && hmode != HOSTC_BLOCKS) sc.reset();
     FrameDesc gd{}; gd.block_size_id = f.desc.block_size_id; gd.block_independent = 1; gd.block_checksum = f.desc.block_checksum;
     uint8_t ghdr[HEADER_MAX]; const uint32_t ghs = header_write(ghdr, gd);
     uint8_t* out = (uint8_t*)dst;
@@ -721,7 +812,7 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* d
         }
         Group& G = groups[g];
         G.src_len = s1 - s0; G.frame_len = ghs + G.src_len + 4 + ix.size(); G.out_cap = (b1 - b0) * (size_t)f.block_size;
-        LANE_CU(ln, cudaSetDevice(ctx->device));
+        LANE_CU(ln, cudaSetDevice(ln->device));
         LANE_CU(ln, ln->stage_in.ensure(G.frame_len + 16));
         LANE_CU(ln, ln->stage_out.ensure(G.out_cap + 16));
         if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // checksum pass over the lane's previous output
@@ -740,16 +831,13 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* d
         b2lz4_ctx* ln = ctx->lanes[g % L];
         const Group& G = groups[g];
         size_t used = 0;
+        LANE_CU(ln, cudaSetDevice(ln->device));
         size_t c = decompress_device_impl(ln, ln->stage_in.p, G.frame_len, ln->stage_out.p, G.out_cap, &used, 0u, SCAN_BATCH, true);
         if (b2lz4_is_error(c)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return c; }
         if (used != G.frame_len) return err_code(E_decompressionFailed);
         if (o + c > cap) return err_code(E_dstMaxSize_tooSmall);
         if (c) LANE_CU(ln, cudaMemcpyAsync(out + o, ln->stage_out.p, c, cudaMemcpyDeviceToHost, ln->st));
-        if (sum && c) {
-            xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>((const uint8_t*)ln->stage_out.p, c, nullptr, nullptr, &ds->xxh);
-            LANE_CU(ln, cudaEventRecord(ln->ev_sum, ctx->st2));
-            ++launches;
-        }
+        if (sum && c) LANE_CU(ln, sc.update(ln, (const uint8_t*)ln->stage_out.p, c, nullptr));   // the lane's decode has completed (host waited)
         launches += ln->stats.kernel_launches; ms_main += ln->stats.ms_main; ms_total += ln->stats.ms_total;
         chains_total += ln->stats.n_chains;
         o += c;
@@ -761,15 +849,18 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* d
     }
     for (size_t g = ngroups > (size_t)L ? ngroups - L : 0; g < ngroups; ++g) { r = complete(g); if (r) return r; }
     for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st));
-    if (sum) {
+    launches += sc.launches;
+    if (sum && multi_dev(ctx)) for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st2));
+    CU(cudaSetDevice(ctx->device));
+    if (sum && !whole) CU(cudaStreamSynchronize(ctx->st2));
+    if (sum && whole) {
         uint32_t h = 0; r = b2lz4_content_checksum(ctx, &h); if (r) return r;
         if (h != f.stored_sum) return err_code(E_contentChecksum_invalid);      // lz4frame.c:1734-1745
     }
-    if (f.desc.has_content_size && f.desc.content_size != o) return err_code(E_frameSize_wrong);   // lz4frame.c:1715-1716
+    if (whole && f.desc.has_content_size && f.desc.content_size != o) return err_code(E_frameSize_wrong);   // lz4frame.c:1715-1716
     ctx->stats.n_blocks = (uint32_t)nb; ctx->stats.n_chains = chains_total; ctx->stats.indexed = f.ix_blocks ? 1u : 0u;
     ctx->stats.kernel_launches = launches; ctx->stats.ms_main = ms_main; ctx->stats.ms_total = ms_total;
-    ctx->stats.bytes_in = n; ctx->stats.bytes_out = o;
-    if (consumed) *consumed = f.consumed;
+    ctx->stats.bytes_in = f.end_blocks; ctx->stats.bytes_out = o;
     return o;
 }
 
@@ -780,28 +871,30 @@ size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, voi
     ctx->stats = b2lz4_stats{};
     if (n == 0) {                                                   // nothing to emit, but the checksum may have to restart
         if ((flags & B2LZ4_STREAM_FIRST) && ctx->prefs.content_checksum) {
-            xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ctx->d_small->xxh);
-            CU(cudaStreamSynchronize(ctx->st));
+            if (multi_dev(ctx)) { r = ensure_lanes(ctx, 1); if (r) return r; SumChain sc{ctx}; sc.reset(); }
+            else {
+                ctx->sum_host = false;
+                xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ctx->d_small->xxh);
+                CU(cudaStreamSynchronize(ctx->st));
+            }
         }
         return 0;
     }
-    size_t bound = b2lz4_compress_bound(n, &ctx->prefs);
-    CU(ctx->stage_in.ensure(n + 16));
-    CU(ctx->stage_out.ensure(bound + 16));
-    CU(cudaMemcpyAsync(ctx->stage_in.p, src, n, cudaMemcpyHostToDevice, ctx->st));
-    r = compress_launch(ctx, (const uint8_t*)ctx->stage_in.p, n, (uint8_t*)ctx->stage_out.p, std::min(bound, cap),
-                        CL_SUM_UPDATE | ((flags & B2LZ4_STREAM_FIRST) ? CL_SUM_RESET : 0u));
-    if (r) return r;
-    r = compress_finish(ctx, n);
-    if (b2lz4_is_error(r)) return r;
-    CU(cudaMemcpyAsync(dst, ctx->stage_out.p, r, cudaMemcpyDeviceToHost, ctx->st));
-    CU(cudaStreamSynchronize(ctx->st));
-    return r;
+    // the batch goes through the same chunk pipeline as a whole frame (lanes, and every device of b2lz4_set_devices)
+    return compress_host_impl(ctx, src, n, dst, cap, (flags & B2LZ4_STREAM_FIRST) ? HOSTC_BLOCKS_FIRST : HOSTC_BLOCKS);
 }
 
 size_t b2lz4_content_checksum(b2lz4_ctx* ctx, uint32_t* out) {
     if (!ctx || !out) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
+    if (ctx->sum_host && ctx->h_xxh) {                              // state in pinned host memory: finish the lanes, digest on the host
+        for (int k = 0; k < ctx->n_lanes; ++k) CU(cudaStreamSynchronize(ctx->lanes[k]->st2));
+        const XxhState s = *ctx->h_xxh;                              // xxhash.c:529-554
+        uint32_t h = s.large ? xxh32_merge(s.v[0], s.v[1], s.v[2], s.v[3]) : s.v[2] + XP5;
+        h += s.total_len;
+        *out = xxh32_tail(h, (const uint8_t*)s.mem, s.memsize);
+        return 0;
+    }
     Small* ds = ctx->d_small;
     CU(cudaStreamSynchronize(ctx->st2));
     xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, nullptr, nullptr);
@@ -853,10 +946,32 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     size_t r = set_device(ctx); if (r) return r;
     Small* ds = ctx->d_small;
     if (flags & B2LZ4_STREAM_FIRST) {
-        ctx->ring_pos = 65536; ctx->ring_hist = 0;
+        ctx->ring_pos = 65536; ctx->ring_hist = 0; ctx->sum_host = false;
         if (info->content_checksum) xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
     }
     if (n == 0) { CU(cudaStreamSynchronize(ctx->st)); return 0; }
+    if (!legacy && info->block_independent) {
+        // independent blocks: the same group pipeline as a whole frame (lanes; every device of b2lz4_set_devices)
+        HostFrame f;
+        f.desc.block_size_id = info->block_size_id; f.desc.block_independent = 1;
+        f.desc.block_checksum = info->block_checksum ? 1u : 0u; f.desc.content_checksum = info->content_checksum ? 1u : 0u;
+        f.block_size = block_size_of(info->block_size_id);
+        const uint8_t* s8 = (const uint8_t*)src;
+        const uint32_t bcs = info->block_checksum ? 4u : 0u;
+        size_t ip = 0; bool good = true;
+        while (ip < n) {
+            if (n - ip < 4) { good = false; break; }
+            const uint32_t w = ld_le32(s8 + ip), cs = w & 0x7FFFFFFFu;
+            if (cs == 0 || cs > f.block_size || n - ip - 4 < (size_t)cs + bcs) { good = false; break; }
+            f.blocks.push_back({ip, w});
+            ip += 4 + (size_t)cs + bcs;
+        }
+        f.end_blocks = n;
+        const size_t per_group = std::max<size_t>(1, pipe_chunk(ctx, f.blocks.size() * (size_t)f.block_size, f.block_size) / f.block_size);
+        if (good && (f.blocks.size() > per_group || multi_dev(ctx))) {
+            return decompress_host_groups(ctx, s8, f, per_group, dst, cap, (flags & B2LZ4_STREAM_FIRST) ? HOSTC_BLOCKS_FIRST : HOSTC_BLOCKS);
+        }
+    }
     // a frame of its own around the batch: header without optional fields, the blocks, an EndMark
     FrameDesc d{};
     d.block_size_id = legacy ? 7u : info->block_size_id; d.block_independent = (legacy || info->block_independent) ? 1u : 0u;

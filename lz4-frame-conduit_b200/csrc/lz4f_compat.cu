@@ -34,6 +34,19 @@ size_t batch_bytes() {                       // B2LZ4_BATCH_MB: uncompressed byt
     return v;
 }
 int device_index() { const char* e = getenv("B2LZ4_DEVICE"); return e ? atoi(e) : 0; }
+// B2LZ4_DEVICES=0,1,2,3: the batches of this stream shard across these GPUs by block index (b2lz4_set_devices)
+size_t apply_devices(b2lz4_ctx* gpu) {
+    const char* e = getenv("B2LZ4_DEVICES");
+    if (!e || !*e) return 0;
+    int devs[16]; int n = 0;
+    for (const char* p = e; *p && n < 16;) {
+        char* q = nullptr; long v = strtol(p, &q, 10);
+        if (q == p) break;
+        devs[n++] = (int)v; p = q;
+        while (*p == ',' || *p == ' ') ++p;
+    }
+    return n ? b2lz4_set_devices(gpu, devs, n) : 0;
+}
 
 struct Pinned {                              // growable pinned host buffer
     uint8_t* p = nullptr; size_t cap = 0;
@@ -122,6 +135,8 @@ size_t LZ4F_compressBegin(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_prefer
     c->batch = batch_bytes();
     if (!c->gpu) {
         size_t r = b2lz4_create(&c->gpu, device_index(), &c->bp);
+        if (b2lz4_is_error(r)) return r;
+        r = apply_devices(c->gpu);
         if (b2lz4_is_error(r)) return r;
     } else {
         size_t r = b2lz4_set_prefs(c->gpu, &c->bp);
@@ -244,6 +259,8 @@ size_t decode_batch(LZ4F_dctx_s* d) {
     if (!d->gpu) {
         b2lz4_prefs bp; b2lz4_default_prefs(&bp); bp.use_index = 0;
         size_t r = b2lz4_create(&d->gpu, device_index(), &bp);
+        if (b2lz4_is_error(r)) return r;
+        r = apply_devices(d->gpu);
         if (b2lz4_is_error(r)) return r;
     }
     const size_t cap = (size_t)d->n_complete * d->info.block_size;
