@@ -25,7 +25,7 @@
  *     (0 = frame complete, else "more input expected") and is resumable at every byte;
  *   - free(NULL) is a no-op; contexts are not thread-safe, distinct contexts are independent.
  * What differs (allowed by the format, lz4_Frame_format.md): frames are always written with independent
- * blocks, LZ4F_default block size means 4 MB, and the encoder works in batches (B2LZ4_BATCH_MB, default
+ * blocks, LZ4F_default block size means 256 KB, and the encoder works in batches (B2LZ4_BATCH_MB, default
  * 64 MiB), so LZ4F_compressBound() is larger than the reference's and output arrives in larger pieces.
  * There is no CPU codec behind these symbols: without a usable CUDA device they return ERROR_cudaFailure.
  */

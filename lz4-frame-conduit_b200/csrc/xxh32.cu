@@ -4,7 +4,7 @@
 // the frame layer uses them: per-block checksums (many independent hashes, one thread each — see
 // xxh32_thread in common.cuh) and the per-frame content checksum.  The content checksum is a single
 // serial recurrence (4 accumulators, xxhash.c:269-275): it cannot be split across threads, so the
-// stream kernel below uses ONE hashing thread fed from shared memory while the rest of the CTA
+// stream kernel below uses ONE hashing warp (a lane per accumulator) fed from shared memory while the rest of the CTA
 // prefetches the next tile; it is meant to run on its own stream, overlapped with the codec kernels.
 #include "common.cuh"
 #include "kernels.h"
@@ -55,7 +55,9 @@ xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t
     __syncthreads();
     const uint64_t pos = s_pos, stripes = s_stripes;
     const uint64_t ntiles = (stripes * 16 + XXH_TILE - 1) / XXH_TILE;
-    uint32_t v1 = s.v[0], v2 = s.v[1], v3 = s.v[2], v4 = s.v[3];
+    // lanes 0..3 of warp 0 own one accumulator each: a stripe then costs the warp one load and three dependent
+    // arithmetic instructions instead of sixteen issue slots of a single thread (the chain latency is what remains)
+    uint32_t acc = s.v[tid & 3u];
     if (ntiles) {
         uint64_t len0 = stripes * 16 < XXH_TILE ? stripes * 16 : XXH_TILE;
         group_copy(tile[0], data + pos, len0, tid, 256);
@@ -69,20 +71,24 @@ xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t
             const uint64_t len2 = (stripes * 16 - off2) < XXH_TILE ? (stripes * 16 - off2) : XXH_TILE;
             if (tid >= 32) group_copy(tile[(t + 1) & 1], data + pos + off2, len2, tid - 32, 224);
         }
-        if (tid == 0) {
-            const uint4* w = (const uint4*)tile[t & 1];
+        if (tid < 4u) {
+            const uint32_t* w = (const uint32_t*)tile[t & 1] + tid;
             const uint32_t ns = (uint32_t)(len >> 4);
-            #pragma unroll 4
-            for (uint32_t i = 0; i < ns; ++i) {
-                uint4 x = w[i];
-                v1 = xxh32_round(v1, x.x); v2 = xxh32_round(v2, x.y);
-                v3 = xxh32_round(v3, x.z); v4 = xxh32_round(v4, x.w);
+            uint32_t i = 0;
+            for (; i + 8 <= ns; i += 8) {
+                uint32_t x[8];
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = w[4u * (i + k)];
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) acc = xxh32_round(acc, x[k]);
             }
+            for (; i < ns; ++i) acc = xxh32_round(acc, w[4u * i]);
         }
         __syncthreads();
     }
+    if (tid < 4u) s.v[tid] = acc;
+    __syncthreads();
     if (tid == 0) {
-        s.v[0] = v1; s.v[1] = v2; s.v[2] = v3; s.v[3] = v4;
         uint64_t done = pos + stripes * 16;
         if (done < n) {                                                       // keep the remainder for later
             uint32_t rem = (uint32_t)(n - done);

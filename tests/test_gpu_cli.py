@@ -61,7 +61,7 @@ def test_cli_identity_with_files_and_preferences(tmp_path, lz4_cli, gen):
     data = gen_bytes(gen, "loglike", (9 << 20) + 777)
     src, mid, back = tmp_path / "in.raw", tmp_path / "in.lz4", tmp_path / "out.raw"
     src.write_bytes(data)
-    for flags, hdr in (([], b"\x60\x70"), (["-B4", "--block-checksum", "--content-checksum"], b"\x74\x40"),
+    for flags, hdr in (([], b"\x60\x50"), (["-B4", "--block-checksum", "--content-checksum"], b"\x74\x40"),
                        (["-B6", "--content-checksum"], b"\x64\x60")):
         run([CLI, str(src), str(mid)] + flags)
         frame = mid.read_bytes()
