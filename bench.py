@@ -205,6 +205,35 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------ our arm
+def max_over_ranks(values, device="cpu"):
+    """Element-wise MAX of per-rank timings over the process group (identity without one): the job is as slow as its
+    slowest rank.  Works on NCCL (device tensors) and gloo (CPU tensors, used by the world_size-2 CPU test)."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t.tolist()]
+
+
+def stream_seed(rank):
+    """Every rank compresses its own stream (weak scaling): seed of rank r's synthetic input."""
+    return 0x10C5 + rank
+
+
+def link_bandwidth(torch, n):
+    """Pinned host <-> device copy bandwidth of this GPU's host link (the end-to-end roofline), GB/s."""
+    h = torch.empty(n, dtype=torch.uint8).pin_memory()
+    d = torch.empty(n, dtype=torch.uint8, device="cuda")
+    out = {}
+    for name, (a, b) in (("h2d", (d, h)), ("d2h", (h, d))):
+        a.copy_(b, non_blocking=True); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); a.copy_(b, non_blocking=True); e1.record(); torch.cuda.synchronize()
+        out[name] = n / (e0.elapsed_time(e1) * 1e-3) / 1e9
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -246,7 +275,7 @@ def main():
 
     # synthetic input: every rank its own stream (weak scaling), generated on the host, moved to HBM once
     host_in = torch.empty(n, dtype=torch.uint8).pin_memory()
-    fill(gen, host_in.data_ptr(), n, args.workload, 0x10C5 + rank)
+    fill(gen, host_in.data_ptr(), n, args.workload, stream_seed(rank))
     d_in = host_in.cuda()
     cap = pkg.compress_bound(n, codec.prefs)
     d_comp = torch.empty(cap, dtype=torch.uint8, device="cuda")
@@ -288,10 +317,7 @@ def main():
     K = args.steps
     dev_ms = (ev["c_total"] + ev["d_total"]) / K             # CUDA events on the codec's own stream
     wall_ms = 1e3 * wall / K
-    t = torch.tensor([wall_ms, dev_ms, ev["c_total"] / K, ev["d_total"] / K], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    wall_ms, dev_ms, c_ms, d_ms = [float(x) for x in t.tolist()]
+    wall_ms, dev_ms, c_ms, d_ms = max_over_ranks([wall_ms, dev_ms, ev["c_total"] / K, ev["d_total"] / K], "cuda")
 
     # ---- end to end through the host-buffer C ABI: pinned host in/out, copies inside the timed region
     e2e = None
@@ -314,13 +340,16 @@ def main():
             ce = step_host()
         barrier()
         e_ms = 1e3 * (time.perf_counter() - t1) / ke
-        te = torch.tensor([e_ms], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e_ms = float(te.item())
+        e_ms = max_over_ranks([e_ms], "cuda")[0]
+        link = link_bandwidth(torch, min(n, 1 << 30))
+        # host-link roofline of the round trip: compress moves U up and C down, decompress C up and U down, the two calls
+        # run one after the other and each direction of the link is used by one transfer at a time
+        bound_ms = 1e3 * (max(n / link["h2d"], ce / link["d2h"]) + max(ce / link["h2d"], n / link["d2h"])) / 1e9
         e2e = {"value": world * n / (e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": n + ce,
                "d2h_bytes_per_step": ce + n, "ms_per_step": e_ms, "steps": ke,
-               "api": "b2lz4_compress_host + b2lz4_decompress_host (pinned host buffers)"}
+               "api": "b2lz4_compress_host + b2lz4_decompress_host (pinned host buffers)",
+               "link": {"h2d_GBps": link["h2d"], "d2h_GBps": link["d2h"], "bound_GBps": world * n / (bound_ms * 1e-3) / 1e9,
+                        "frac": (world * n / (e_ms * 1e-3)) / (world * n / (bound_ms * 1e-3))}}
 
     if rank != 0:
         if world > 1:
@@ -335,8 +364,19 @@ def main():
     rf_c = {"kernel": "find_emit_kernel", "bound": "hbm", "achieved": alg / (ev["c_main"] / K * 1e-3) / 1e9,
             "peak": peak, "unit": "GB/s", "traffic": None, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": alg, "avg_launch_ms": ev["c_main"] / K}
+    traffic = {}
+    try:                                                      # measured DRAM bytes per launch (one ncu --set full capture per kernel)
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tj = json.load(f)
+        c = tj.get("config", {})
+        if (c.get("workload") == args.workload and c.get("size_mib") == args.size_mib and c.get("block_id") == args.block_id
+                and c.get("sub_log2") == args.sub_log2):
+            traffic = tj
+    except Exception:
+        pass
     for r in (rf_d, rf_c):
         r["frac"] = r["achieved"] / peak
+        r["traffic"] = traffic.get(r["kernel"])
     dominant, other = (rf_c, rf_d) if ev["c_main"] >= ev["d_main"] else (rf_d, rf_c)
 
     cpu = None

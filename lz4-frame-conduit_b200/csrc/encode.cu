@@ -405,20 +405,22 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 
 // ------------------------------------------------------------------------------------------------
 // layout: per-block stitch sizes, stored decision, frame offsets (scan), header / EndMark / index.
-// One CTA of 1024 threads.
+// One CTA of LAYOUT_THREADS threads — no more than one match-finder CTA, so that it can start in any slot a retiring
+// match-finder CTA of ANOTHER chunk frees (the host-buffer pipeline keeps several chunks in flight on different streams).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(LAYOUT_THREADS)
 layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict__ places,
               BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst, uint64_t dst_cap,
               EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket, uint8_t* __restrict__ idx_frag)
 {
-    __shared__ uint64_t part_bytes[1024];
-    __shared__ uint32_t part_chain[1024];
+    constexpr uint32_t NT = LAYOUT_THREADS;
+    __shared__ uint64_t part_bytes[NT];
+    __shared__ uint32_t part_chain[NT];
     __shared__ EncodeResult s_res;
     const uint32_t tid = threadIdx.x;
     const uint32_t nb = P.n_blocks;
     const uint32_t bc = P.block_checksum ? 4u : 0u;
-    const uint32_t per = (nb + 1023u) / 1024u;
+    const uint32_t per = (nb + NT - 1u) / NT;
     const uint32_t b0 = tid * per < nb ? tid * per : nb, b1 = (b0 + per < nb) ? b0 + per : nb;
     if (tid == 0) *ticket = 0;
 
@@ -452,7 +454,7 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
     if (tid == 0) {
         const uint32_t hs = P.write_header ? (7u + (P.desc.has_content_size ? 8u : 0u) + (P.desc.has_dict_id ? 4u : 0u)) : 0u;
         uint64_t run = hs; uint32_t rc = 0;
-        for (int i = 0; i < 1024; ++i) {
+        for (uint32_t i = 0; i < NT; ++i) {
             uint64_t t = part_bytes[i]; uint32_t c = part_chain[i];
             part_bytes[i] = run; part_chain[i] = rc; run += t; rc += c;
         }

@@ -316,7 +316,7 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
         ++launches;
     }
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
-    layout_kernel<<<1, 1024, 0, ctx->st>>>(P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p,
+    layout_kernel<<<1, LAYOUT_THREADS, 0, ctx->st>>>(P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p,
                                            (BlockPlace*)ctx->bplaces.p, d_dst, cap, &ds->eres, &ds->ticket_enc,
                                            (flags & CL_INDEX_FRAGMENT) ? (uint8_t*)ctx->idx_frag.p : nullptr);
     ++launches;

@@ -26,6 +26,7 @@ constexpr int ENC_CTAS_PER_SM = B2_ENC_CTAS;   // resident CTAs per SM the kerne
 #define B2_ENC_HLOG 13
 #endif
 constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 8192-entry u16 hash table per warp (16 KB)
+constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
                   SCAN_LEGACY = 8u };   // blocks of a legacy frame (lz4_Frame_format.md:338-386): 8 MB, always compressed, no flag bit
 constexpr uint32_t LEGACY_BLOCK = 8u << 20;

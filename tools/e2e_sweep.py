@@ -16,9 +16,10 @@ assert torch.equal(h_in, h_b)
 K = 4
 t0 = time.perf_counter()
 for _ in range(K): cs = c.compress_host_ptr(h_in.data_ptr(), n, h_c.data_ptr(), cap)
-t1 = time.perf_counter()
+t1 = time.perf_counter(); sc = c.stats()
 for _ in range(K): c.decompress_host_ptr(h_c.data_ptr(), cs, h_b.data_ptr(), n)
-t2 = time.perf_counter()
+t2 = time.perf_counter(); sd = c.stats()
+print(f"  compress: sum over chunks of find_emit {sc.ms_main:.1f} ms, of whole chunk streams {sc.ms_total:.1f} ms, launches {sc.kernel_launches}; decompress: decode {sd.ms_main:.1f} ms, total {sd.ms_total:.1f} ms")
 # plain copies for reference
 d = torch.empty(n, dtype=torch.uint8, device="cuda"); torch.cuda.synchronize()
 t3 = time.perf_counter(); d.copy_(h_in, non_blocking=True); torch.cuda.synchronize(); t4 = time.perf_counter()
