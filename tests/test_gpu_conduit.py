@@ -1,0 +1,179 @@
+"""The streaming conduit mirror (lz4-frame-conduit_b200/conduit.py: Conduit.hsc's conduits, call for call, on our LZ4F_*
+symbols) and the BASELINE.json configurations that are parity cases rather than bench lines (configs 1, 4, 5)."""
+import os
+import random
+import subprocess
+
+import pytest
+
+from conftest import ROOT, gen_bytes, golden_bytes, orc_decode, ref_conduit_decode
+
+pytestmark = pytest.mark.gpu
+
+
+def _lz4(lz4_cli, args, data):
+    p = subprocess.run([lz4_cli] + args, input=data, capture_output=True, timeout=600)
+    assert p.returncode == 0, p.stderr.decode()[-300:]
+    return p.stdout
+
+
+# ------------------------------------------------------------------ conduit mirror
+def test_conduit_identity_any_chunking(pkg, gen, ref, lz4_cli):
+    """QuickCheck identity (test/Main.hs:114-119) plus: the frame does not depend on how the input was chunked, the three
+    compress variants emit the same bytes (Conduit.hsc:327-333, 356-363), reference conduit and stock CLI decode them."""
+    cd = pkg.conduit
+    rnd = random.Random(5)
+    data = gen_bytes(gen, "loglike", (11 << 20) + 321)
+    frames = set()
+    for chunk in (1 << 20, 16384, 100003):
+        frames.add(b"".join(cd.compress(pkg.bs_chunks_of(chunk, data))))
+    frames.add(b"".join(cd.compress_yield_immediately(pkg.bs_chunks_of(70000, data))))
+    frames.add(b"".join(cd.compress_with_out_buffer_size(1 << 20, [data])))
+    assert len(frames) == 1
+    frame = frames.pop()
+    assert frame[:7] == bytes.fromhex("04224d186050fb") or frame[:6] == bytes.fromhex("04224d186050")    # independent, 256 KB blocks
+    got, used = ref_conduit_decode(ref, frame, len(data) + 64)
+    assert got == data and used == len(frame)
+    assert _lz4(lz4_cli, ["-d", "-c"], frame) == data
+    for chunk in (len(frame), 65536, 4099, 7):
+        if chunk == 7 and len(frame) > (1 << 20):
+            parts = pkg.bs_chunks_of(7, frame[:4096]) + [frame[4096:]]                                   # tiny chunks across the header
+        else:
+            parts = pkg.bs_chunks_of(chunk, frame)
+        assert b"".join(cd.decompress(parts)) == data
+    for _ in range(25):                                                                                   # small arbitrary strings
+        n = rnd.randrange(0, 20000)
+        s = bytes(rnd.choice(b"abcdefgh \n") for _ in range(n))
+        fr = b"".join(cd.compress(pkg.bs_chunks_of(rnd.randrange(1, 5000), s)))
+        assert b"".join(cd.decompress(pkg.bs_chunks_of(rnd.randrange(1, 3000), fr))) == s
+    assert b"".join(cd.decompress([b"".join(cd.compress([]))])) == b""
+
+
+def test_conduit_preferences_and_errors(pkg, gen, lz4_cli, manifest):
+    cd = pkg.conduit
+    data = gen_bytes(gen, "textlike", 3 << 20)
+    p = cd.lz4_default_preferences()
+    p.blockSizeID, p.blockChecksumFlag, p.contentChecksumFlag = 4, 1, 1
+    frame = b"".join(cd.compress([data], p))
+    assert frame[4:6] == b"\x74\x40"                                      # same FLG/BD as `lz4 -B4 -BX`
+    assert _lz4(lz4_cli, ["-d", "-c"], frame) == data
+    assert b"".join(cd.decompress([frame, b"trailing bytes stay unread"])) == data
+    with pytest.raises(pkg.Lz4FrameError, match="stream ended before EndMark"):            # Conduit.hsc:689
+        list(cd.decompress([frame[:-9]]))
+    with pytest.raises(pkg.Lz4FrameError, match="not enough bytes for header"):            # Conduit.hsc:615-616
+        list(cd.decompress([b"\x04\x22"]))
+    bad = bytearray(frame); bad[len(bad) // 3] ^= 0x10
+    with pytest.raises(pkg.Lz4FrameError, match="lz4frame error: ERROR_"):
+        list(cd.decompress([bytes(bad)]))
+    # frames the reference made (linked blocks) through the streaming decompress
+    for key in ("numbers", "datagen200k"):
+        if key in manifest:
+            e = manifest[key]
+            assert b"".join(cd.decompress(pkg.bs_chunks_of(5000, golden_bytes(e["frames"]["conduit"]["file"])))) == golden_bytes(e["raw"])
+
+
+# ------------------------------------------------------------------ config 1: 64 MiB text-like, reference conduit on the other side
+def test_config1_64MiB_textlike_against_the_reference_conduit(pkg, replay, ref, datagen, lz4_cli):
+    """BASELINE.json config 1: the reference's own generator (datagen -g64MB -s1), compressed by the reference conduit
+    (linked 64 KB blocks, what it really emits — SURVEY appendix C.1) and decoded by us; compressed by us with 64 KB
+    independent blocks and decoded by the reference conduit and the stock CLI."""
+    assert datagen and ref
+    n = 64 << 20
+    data = subprocess.run([datagen, f"-g{n}", "-s1"], capture_output=True, check=True).stdout
+    assert len(data) == n
+    import ctypes as C
+    cap = n + (n >> 7) + (1 << 20)
+    out = C.create_string_buffer(cap)
+    r = ref.ref_conduit_compress(data, n, out, cap, 32768, 0)
+    assert r < (1 << 62)
+    ref_frame = out.raw[:r]
+    assert ref_frame[:7] == bytes.fromhex("04224d184040c0")
+    assert b"".join(pkg.conduit.decompress(pkg.bs_chunks_of(1 << 20, ref_frame))) == data
+    with pkg.Codec(0) as c:
+        got, used = c.decompress_bytes(ref_frame, max_out=n)
+        assert got == data and used == len(ref_frame)
+    p = pkg.conduit.lz4_default_preferences(); p.blockSizeID = 4
+    ours = b"".join(pkg.conduit.compress(pkg.bs_chunks_of(1 << 20, data), p))
+    got, used = ref_conduit_decode(ref, ours, n + 64)
+    assert got == data and used == len(ours)
+    assert _lz4(lz4_cli, ["-d", "-c"], ours) == data
+    print(f"config 1: reference conduit {len(ref_frame)} B (linked 64 KB), ours {len(ours)} B (independent 64 KB), "
+          f"{100.0 * (len(ours) / len(ref_frame) - 1):+.2f} %")
+
+
+# ------------------------------------------------------------------ config 4: frames made by the stock CLI
+SIZES = [0, 1, 12, 13, 65535, 65536, 65537, 1200007, 4194304, 4194305]
+FLAGS = [[], ["-B4", "-BX"], ["-B5", "-BX"], ["-B6", "-BX"], ["-B7", "-BX"], ["--no-frame-crc"], ["--content-size"],
+         ["-B4", "-BD"], ["-B7", "-BD", "-BX", "--content-size"]]
+
+
+def test_config4_stock_cli_frames_bit_exact(pkg, gen, oracle, lz4_cli):
+    """Every flag set x size of SURVEY §8d config 4, generated live by the stock CLI: decoded bytes, frame info and
+    consumed size must equal the oracle's; a flipped bit in a checksummed frame must be reported, by name."""
+    assert lz4_cli
+    big = gen_bytes(gen, "textlike", SIZES[-1], 9)
+    shapes = {"text": big, "zeros": bytes(SIZES[-1]), "random": gen_bytes(gen, "random", SIZES[-1], 10)}
+    n_frames = n_cli_bug = 0
+    with pkg.Codec(0) as c:
+        for flags in FLAGS:
+            for size in SIZES:
+                for shape, src in shapes.items():
+                    if shape != "text" and size not in (13, 65537, 4194305):
+                        continue
+                    data = src[:size]
+                    pr = subprocess.run([lz4_cli, "-c"] + flags, input=data, capture_output=True, timeout=600)
+                    if pr.returncode != 0:                   # v1.9.2's own CLI cannot write some stored 64 KB blocks (its Error 31)
+                        assert b"dstMaxSize_tooSmall" in pr.stderr and "-B4" in flags, pr.stderr
+                        n_cli_bug += 1
+                        continue
+                    frame = pr.stdout
+                    want, used_o = orc_decode(oracle, frame, size + 16)
+                    assert want == data
+                    got, used = c.decompress_bytes(frame, max_out=size)
+                    assert got == data and used == used_o == len(frame), (flags, size, shape)
+                    n_frames += 1
+        # corrupted checksums (content checksum is on unless --no-frame-crc; -BX adds block checksums)
+        data = big[:1200007]
+        for flags, name in (([], "ERROR_contentChecksum_invalid"), (["-B4", "-BX"], "ERROR_blockChecksum_invalid")):
+            frame = bytearray(_lz4(lz4_cli, ["-c"] + flags, data))
+            frame[-1] ^= 0x01 if not flags else 0x00
+            if flags:
+                frame[7 + 4 + 100] ^= 0x20                  # inside the first block's data
+            with pytest.raises(pkg.Lz4FrameError) as ei:
+                c.decompress_bytes(bytes(frame), max_out=len(data))
+            assert ei.value.name in (name, "ERROR_decompressionFailed"), ei.value.name
+    assert n_frames > 100
+    print(f"config 4: {n_frames} stock-CLI frames decoded bit-exactly ({n_cli_bug} inputs the stock CLI could not compress itself)")
+
+
+# ------------------------------------------------------------------ config 5: edge mix at full size, device-resident
+def test_config5_full_size_random_and_zeros(pkg):
+    """4 GiB incompressible + 4 GiB zeros (B2_EDGE_GIB overrides), 4 MB blocks, device-resident: every random block must
+    be stored (header word 0x80400000, frame = input + 4 B per block + 15), the zero stream must shrink > 200 x, both
+    round trips bit-exact — size-independent properties at BASELINE.json's size."""
+    import torch
+    gib = float(os.environ.get("B2_EDGE_GIB", "4"))
+    n = int(gib * (1 << 30))
+    with pkg.Codec(0, block_size_id=7) as c:
+        cap = pkg.compress_bound(n, c.prefs)
+        d_comp = torch.empty(cap, dtype=torch.uint8, device="cuda")
+        d_back = torch.empty(n, dtype=torch.uint8, device="cuda")
+        g = torch.Generator(device="cuda"); g.manual_seed(7)
+        d_in = torch.empty(n, dtype=torch.uint8, device="cuda")
+        step = 1 << 28
+        for i in range(0, n, step):
+            d_in[i:i + step] = torch.randint(0, 256, (min(step, n - i),), dtype=torch.uint8, device="cuda", generator=g)
+        torch.cuda.synchronize()                                   # the codec runs on its own (non-blocking) stream
+        cs = c.compress_device(d_in.data_ptr(), n, d_comp.data_ptr(), cap)
+        nb = (n + (4 << 20) - 1) >> 22
+        assert cs == 7 + n + 4 * nb + 4
+        words = d_comp[7:7 + 4].cpu().numpy().tobytes()
+        assert words == bytes.fromhex("00004080")                         # 0x80400000 little endian: stored, 4 MB
+        r, used = c.decompress_device(d_comp.data_ptr(), cs, d_back.data_ptr(), n)
+        assert r == n and used == cs and torch.equal(d_back, d_in)
+        d_in.zero_(); torch.cuda.synchronize()
+        cs = c.compress_device(d_in.data_ptr(), n, d_comp.data_ptr(), cap)
+        assert n / cs > 200
+        d_back.fill_(255); torch.cuda.synchronize()
+        r, used = c.decompress_device(d_comp.data_ptr(), cs, d_back.data_ptr(), n)
+        assert r == n and used == cs and int(d_back.max().item()) == 0
