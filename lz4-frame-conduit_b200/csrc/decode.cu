@@ -31,11 +31,77 @@ __device__ const uint8_t* find_index(const uint8_t* src, uint64_t n, uint64_t* p
     return payload;
 }
 
+// Serial walk over the block header words of a frame (lz4frame.c:1470-1500) by ONE thread: fills the block / piece /
+// chain tables and the frame summary `s`.  When `progress` is given (chain-per-block layout only) the number of chains
+// published so far is stored there after every block, behind a fence, so that decoding warps of the same kernel can
+// start on block b while the walk is still hopping through the headers that follow it.
+__device__ __noinline__ void walk_blocks(const uint8_t* __restrict__ src, uint64_t n, uint32_t mode, FrameIndex& s,
+                            BlockRef* blocks, uint32_t cap_blocks, Piece* pieces, uint32_t cap_pieces, Chain* chains,
+                            uint32_t* stored_list, volatile uint32_t* progress)
+{
+    const uint32_t bc = s.desc.block_checksum ? 4u : 0u;
+    const uint32_t cc = s.desc.content_checksum ? 4u : 0u;
+    const bool per_block = s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN);
+    uint64_t ip = s.desc.header_size;
+    uint32_t nb = 0, nstored = 0;
+    Err err = OK;
+    for (;;) {
+        if (n - ip < 4) { err = E_noEndMark; break; }
+        uint32_t w = ld_le32_dev(src + ip); ip += 4;
+        uint32_t cs = w & 0x7FFFFFFFu;
+        if (cs == 0) break;                                      // EndMark
+        if (mode & SCAN_LEGACY) {                                // no stored flag; a block may be as large as LZ4_compressBound(8 MB)
+            if ((w >> 31) || cs > LEGACY_BLOCK + LEGACY_BLOCK / 255u + 16u) { err = E_maxBlockSize_invalid; break; }
+        } else
+        if (cs > s.block_size) { err = E_maxBlockSize_invalid; break; }
+        if (n - ip < (uint64_t)cs + bc) { err = E_noEndMark; break; }
+        if (nb < cap_blocks && nb < cap_pieces) {
+            if (progress) {
+                // decoder-side walk: one 16-byte raw entry per block (in the chain slot); the warp that decodes the block
+                // expands it into the BlockRef / Piece / Chain the later kernels read (expand_walk_entry)
+                *(uint4*)(chains + nb) = make_uint4((uint32_t)ip, (uint32_t)(ip >> 32), cs, w >> 31);
+                if (w >> 31) stored_list[nstored++] = nb;
+                if ((nb & 7u) == 7u) { __threadfence(); *progress = nb + 1u; }      // publish in groups: a fence per block would cost more than the hop
+            } else {
+                BlockRef br; br.src_off = ip; br.csize = cs; br.stored = w >> 31;
+                br.dst_off = (uint64_t)nb * s.block_size; br.usize = 0; br.pad = 0;
+                blocks[nb] = br;
+                Piece pc; pc.src_off = ip; pc.src_len = cs;
+                pc.flags = PIECE_ENDS_BLOCK | (br.stored ? PIECE_STORED : 0u);
+                pc.dst_len = 0; pc.block = nb; pc.dst_rel = 0; pc.pad = 0;
+                if (per_block) {
+                    Chain ch; ch.dst_off = br.dst_off; ch.first_piece = nb; ch.n_pieces = 1; chains[nb] = ch;
+                    if (br.stored) { pc.flags |= PIECE_BULK; stored_list[nstored++] = nb; }
+                }
+                pieces[nb] = pc;
+            }
+        }
+        ++nb;
+        ip += (uint64_t)cs + bc;
+    }
+    if (progress) { __threadfence(); *progress = nb < cap_blocks ? nb : cap_blocks; }
+    if (err == OK && cc) {
+        if (n - ip < 4) err = E_noEndMark;
+        else { s.stored_content_checksum = ld_le32_dev(src + ip); ip += 4; }
+    }
+    s.need_blocks = nb; s.need_pieces = nb;
+    if (err == OK && (nb > cap_blocks || nb > cap_pieces)) err = E_allocation_failed;
+    s.err = err;
+    s.n_blocks = nb; s.n_pieces = nb; s.n_stored = nstored;
+    s.consumed = ip; s.consumed_with_index = ip;
+    s.total_out = (uint64_t)nb * s.block_size;                   // upper bound
+    if (per_block) { s.n_chains = nb; s.layout_known = 0; }
+    else {
+        s.n_chains = nb ? 1u : 0u; s.layout_known = 0;
+        if (nb && err == OK) { Chain ch; ch.dst_off = 0; ch.first_piece = 0; ch.n_pieces = nb; chains[0] = ch; }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap, uint32_t mode,
                   FrameIndex* __restrict__ fi, BlockRef* __restrict__ blocks, uint32_t cap_blocks,
                   Piece* __restrict__ pieces, uint32_t cap_pieces, Chain* __restrict__ chains,
-                  uint32_t* __restrict__ stored_list)
+                  uint32_t* __restrict__ stored_list, uint32_t* __restrict__ walk)
 {
     __shared__ FrameIndex s;
     __shared__ uint32_t s_nstored;
@@ -159,51 +225,14 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
     }
 
     if (tid == 0) {
-        // ---- serial walk over the block header words (lz4frame.c:1470-1500)
-        uint64_t ip = s.desc.header_size;
-        uint32_t nb = 0;
-        Err err = OK;
-        for (;;) {
-            if (n - ip < 4) { err = E_noEndMark; break; }
-            uint32_t w = ld_le32_dev(src + ip); ip += 4;
-            uint32_t cs = w & 0x7FFFFFFFu;
-            if (cs == 0) break;                                      // EndMark
-            if (mode & SCAN_LEGACY) {                                // no stored flag; a block may be as large as LZ4_compressBound(8 MB)
-                if ((w >> 31) || cs > LEGACY_BLOCK + LEGACY_BLOCK / 255u + 16u) { err = E_maxBlockSize_invalid; break; }
-            } else
-            if (cs > s.block_size) { err = E_maxBlockSize_invalid; break; }
-            if (n - ip < (uint64_t)cs + bc) { err = E_noEndMark; break; }
-            if (nb < cap_blocks && nb < cap_pieces) {
-                BlockRef br; br.src_off = ip; br.csize = cs; br.stored = w >> 31;
-                br.dst_off = (uint64_t)nb * s.block_size; br.usize = 0; br.pad = 0;
-                blocks[nb] = br;
-                Piece pc; pc.src_off = ip; pc.src_len = cs;
-                pc.flags = PIECE_ENDS_BLOCK | (br.stored ? PIECE_STORED : 0u);
-                pc.dst_len = 0; pc.block = nb; pc.dst_rel = 0; pc.pad = 0;
-                if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) {
-                    Chain ch; ch.dst_off = br.dst_off; ch.first_piece = nb; ch.n_pieces = 1; chains[nb] = ch;
-                    if (br.stored) { pc.flags |= PIECE_BULK; stored_list[s_nstored++] = nb; }
-                }
-                pieces[nb] = pc;
-            }
-            ++nb;
-            ip += (uint64_t)cs + bc;
+        if ((mode & SCAN_OVERLAP_WALK) && s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) {
+            // the walk is left to the decoder kernel, which runs it next to the decoding warps (walk_blocks below)
+            s.walk_pending = 1;
+            walk[0] = 0; walk[1] = 0;
+            *fi = s;
+            return;
         }
-        if (err == OK && cc) {
-            if (n - ip < 4) err = E_noEndMark;
-            else { s.stored_content_checksum = ld_le32_dev(src + ip); ip += 4; }
-        }
-        s.need_blocks = nb; s.need_pieces = nb;
-        if (err == OK && (nb > cap_blocks || nb > cap_pieces)) err = E_allocation_failed;
-        s.err = err;
-        s.n_blocks = nb; s.n_pieces = nb; s.n_stored = s_nstored;
-        s.consumed = ip; s.consumed_with_index = ip;
-        s.total_out = (uint64_t)nb * s.block_size;                   // upper bound
-        if (s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) { s.n_chains = nb; s.layout_known = 0; }
-        else {
-            s.n_chains = nb ? 1u : 0u; s.layout_known = 0;
-            if (nb && err == OK) { Chain ch; ch.dst_off = 0; ch.first_piece = 0; ch.n_pieces = nb; chains[0] = ch; }
-        }
+        walk_blocks(src, n, mode, s, blocks, cap_blocks, pieces, cap_pieces, chains, stored_list, nullptr);
         *fi = s;
     }
 }
@@ -547,14 +576,24 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
     return err ? err : (paused ? DEC_PAUSED : 0u);
 }
 
+// table entries are read past L1: in walk_pending mode another CTA of this very kernel has just written them
+template <typename T>
+__device__ __forceinline__ T ld_cg(const T* p) {
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    T v;
+    #pragma unroll
+    for (uint32_t i = 0; i < sizeof(T) / 16; ++i) ((uint4*)&v)[i] = __ldcg((const uint4*)p + i);
+    return v;
+}
+
 #ifndef B2_DEC_MINCTAS
 #define B2_DEC_MINCTAS 4      // 8 warps x 4 CTAs: 64 registers per thread, 32 warps per SM
 #endif
 __global__ void __launch_bounds__(DEC_WARPS * 32, B2_DEC_MINCTAS)
-decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint64_t dst_cap,
-                     const FrameIndex* __restrict__ fi, const BlockRef* __restrict__ blocks,
-                     const Piece* __restrict__ pieces, const Chain* __restrict__ chains,
-                     PieceOut* __restrict__ outs, uint32_t* __restrict__ ticket, uint32_t hist)
+decode_chains_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __restrict__ dst, uint64_t dst_cap, uint32_t mode,
+                     FrameIndex* fi, BlockRef* blocks, Piece* pieces, Chain* chains, uint32_t cap_tables,
+                     uint32_t* stored_list, PieceOut* __restrict__ outs, uint32_t* __restrict__ ticket, uint32_t* walk,
+                     uint32_t hist)
 {
     // hist = bytes of earlier output of the same linked-block frame that lie directly in front of dst
     // (streaming decode in batches: lz4frame.c:1286-1349 keeps the same 64 KB)
@@ -567,25 +606,66 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
         my_win[272u + 256u * t + x] = (uint8_t)x;
     }
     __syncwarp();
-    const uint8_t* const src_end = src + fi->consumed_with_index;
-    const uint32_t n_chains = fi->n_chains;
+    // walk_pending: the block headers have not been walked yet (plain frame, no index).  Warp 0 of CTA 0 does it now, with
+    // one thread, publishing every block as it is found; all other warps start decoding published blocks at once, so the
+    // serial hops through the headers (one DRAM round trip each) hide behind the decoding instead of preceding it.
+    // CTA 0 is resident from the start of the grid, and the walker never waits for anybody: no deadlock.
+    const bool pending = fi->walk_pending != 0;
     const uint32_t block_size = fi->block_size;
     const bool linked = !fi->desc.block_independent;
+    if (pending && blockIdx.x == 0 && threadIdx.x < 32u) {
+        if (lane == 0) {
+            FrameIndex s = *fi;
+            walk_blocks(src, n_src, mode, s, blocks, cap_tables, pieces, cap_tables, chains, stored_list, walk);
+            s.walk_pending = 2;                                       // walked inside the decoder
+            *fi = s;
+            __threadfence();
+            ((volatile uint32_t*)walk)[1] = 1u;                       // done: walk[0] is final
+        }
+        __syncwarp();
+    }
+    const uint8_t* const src_end = pending ? src + n_src : src + fi->consumed_with_index;
+    const uint32_t n_chains = pending ? 0u : fi->n_chains;
     for (;;) {
         uint32_t c = 0;
         if (lane == 0) c = atomicAdd(ticket, 1u);
         c = __shfl_sync(FULL_MASK, c, 0);
-        if (c >= n_chains) break;
-        const Chain ch = chains[c];
+        if (pending) {
+            uint32_t ok = 0;
+            if (lane == 0) {
+                volatile uint32_t* w = (volatile uint32_t*)walk;
+                for (;;) {
+                    if (c < w[0]) { ok = 1; break; }
+                    if (w[1]) { ok = c < w[0] ? 1u : 0u; break; }
+                    __nanosleep(400);
+                }
+                __threadfence();
+            }
+            ok = __shfl_sync(FULL_MASK, ok, 0);
+            if (!ok) break;
+        } else if (c >= n_chains) break;
+        Chain ch;
+        if (pending) {
+            // raw walk entry {src_off, csize, stored} -> the tables the later kernels (and the loop below) read
+            const uint4 e = __ldcg((const uint4*)(chains + c));
+            BlockRef br; br.src_off = (uint64_t)e.x | ((uint64_t)e.y << 32); br.csize = e.z; br.stored = e.w;
+            br.dst_off = (uint64_t)c * block_size; br.usize = 0; br.pad = 0;
+            Piece pc; pc.src_off = br.src_off; pc.src_len = e.z;
+            pc.flags = PIECE_ENDS_BLOCK | (e.w ? (PIECE_STORED | PIECE_BULK) : 0u);
+            pc.dst_len = 0; pc.block = c; pc.dst_rel = 0; pc.pad = 0;
+            ch.dst_off = br.dst_off; ch.first_piece = c; ch.n_pieces = 1;
+            if (lane == 0) { blocks[c] = br; pieces[c] = pc; chains[c] = ch; }
+            __syncwarp();
+        } else ch = ld_cg(chains + c);
         uint64_t op = ch.dst_off;
         const uint64_t chain_start = ch.dst_off;
         bool dead = false;
         for (uint32_t k = 0; k < ch.n_pieces; ++k) {
             const uint32_t pi = ch.first_piece + k;
-            const Piece pc = pieces[pi];
+            const Piece pc = ld_cg(pieces + pi);
             PieceOut po; po.out_len = 0; po.err = 0;
             if (dead) { po.err = E_decompressionFailed; if (lane == 0) outs[pi] = po; continue; }
-            const BlockRef br = blocks[pc.block];
+            const BlockRef br = ld_cg(blocks + pc.block);
             // output window of the owning block (the reference hands maxBlockSize as capacity, lz4frame.c:1670)
             uint64_t blk_out = (pc.flags & PIECE_EXACT) ? br.dst_off : op;
             uint64_t oend = blk_out + block_size;

@@ -59,7 +59,7 @@ struct FrameIndex {
     uint32_t need_blocks;     // table sizes the scan wanted (for the retry after E_allocation_failed)
     uint32_t need_pieces;
     uint32_t n_stored;        // stored blocks listed for copy_stored_kernel
-    uint32_t pad0;
+    uint32_t walk_pending;    // 1 = the serial walk over the block headers is left to the decoder kernel (2 = done there)
     FrameDesc desc;
 };
 

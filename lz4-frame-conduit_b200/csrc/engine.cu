@@ -51,6 +51,7 @@ struct Small {                 // small device-side state, mirrored to pinned ho
     EncodeResult eres;
     XxhState xxh;
     uint32_t ticket_dec, ticket_enc, crc_bad, hash_out;
+    uint32_t walk[2];          // decoder-side block walk: chains published so far, done flag
 };
 
 }  // namespace
@@ -383,15 +384,15 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
     CU(cudaMemsetAsync(&ds->crc_bad, 0xFF, sizeof(uint32_t), ctx->st));
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
     frame_scan_kernel<<<1, 256, 0, ctx->st>>>(d_src, n, cap, mode, &ds->fi, (BlockRef*)ctx->blocks.p, cap_tables,
-                                              (Piece*)ctx->pieces.p, cap_tables, (Chain*)ctx->chains.p, (uint32_t*)ctx->stored.p);
-    verify_block_checksums_kernel<<<std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st>>>(
-        d_src, &ds->fi, (const BlockRef*)ctx->blocks.p, &ds->crc_bad);
+                                              (Piece*)ctx->pieces.p, cap_tables, (Chain*)ctx->chains.p, (uint32_t*)ctx->stored.p, ds->walk);
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
     decode_chains_kernel<<<ctx->sm_count * (64 / DEC_WARPS), DEC_WARPS * 32, 0, ctx->st>>>(
-        d_src, d_dst, cap, &ds->fi, (const BlockRef*)ctx->blocks.p, (const Piece*)ctx->pieces.p,
-        (const Chain*)ctx->chains.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec, hist);
+        d_src, n, d_dst, cap, mode, &ds->fi, (BlockRef*)ctx->blocks.p, (Piece*)ctx->pieces.p, (Chain*)ctx->chains.p, cap_tables,
+        (uint32_t*)ctx->stored.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec, ds->walk, hist);
     copy_stored_kernel<<<ctx->sm_count * 8, 256, 0, ctx->st>>>(d_src, d_dst, cap, &ds->fi, (const Piece*)ctx->pieces.p,
                                                              (const Chain*)ctx->chains.p, (const uint32_t*)ctx->stored.p);
+    verify_block_checksums_kernel<<<std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st>>>(
+        d_src, &ds->fi, (const BlockRef*)ctx->blocks.p, &ds->crc_bad);
     CU(cudaEventRecord(ctx->ev[2], ctx->st));
     decode_finalize_kernel<<<1, 256, 0, ctx->st>>>(&ds->fi, (const Piece*)ctx->pieces.p, (const PieceOut*)ctx->outs.p,
                                                    &ds->crc_bad, &ds->dres, &ds->ticket_dec);
@@ -421,7 +422,7 @@ static uint32_t tables_for(size_t n, size_t cap) {
 // queues the first decode attempt on ctx->st without waiting; decompress_device_impl(..., launched0 = true) completes it
 static size_t decompress_begin(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, uint32_t hist, uint32_t mode0) {
     ctx->stats = b2lz4_stats{};
-    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u);
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK;
     return decompress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, mode, tables_for(n, cap), hist);
 }
 size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed) {
@@ -437,7 +438,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
     static uint8_t* dummy = nullptr;
     uint8_t* dst = (uint8_t*)d_dst;
     if (!dst) { if (!dummy) CU(cudaMalloc(&dummy, 256)); dst = dummy; }
-    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u);
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK;
     uint32_t cap_tables = tables_for(n, cap);
     for (int attempt = 0; attempt < 4; ++attempt) {
         if (!(launched0 && attempt == 0)) {

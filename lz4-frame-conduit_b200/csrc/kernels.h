@@ -28,18 +28,19 @@ constexpr int ENC_CTAS_PER_SM = B2_ENC_CTAS;   // resident CTAs per SM the kerne
 constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 8192-entry u16 hash table per warp (16 KB)
 constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
-                  SCAN_LEGACY = 8u };   // blocks of a legacy frame (lz4_Frame_format.md:338-386): 8 MB, always compressed, no flag bit
+                  SCAN_LEGACY = 8u,
+                  SCAN_OVERLAP_WALK = 16u };  // plain independent-block frames: walk the block headers inside the decoder kernel   // blocks of a legacy frame (lz4_Frame_format.md:338-386): 8 MB, always compressed, no flag bit
 constexpr uint32_t LEGACY_BLOCK = 8u << 20;
 
 // ---- decode
 __global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_cap, uint32_t mode,
                                   FrameIndex* fi, BlockRef* blocks, uint32_t cap_blocks,
-                                  Piece* pieces, uint32_t cap_pieces, Chain* chains, uint32_t* stored_list);
+                                  Piece* pieces, uint32_t cap_pieces, Chain* chains, uint32_t* stored_list, uint32_t* walk);
 __global__ void copy_stored_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap, const FrameIndex* fi,
                                    const Piece* pieces, const Chain* chains, const uint32_t* stored_list);
-__global__ void decode_chains_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap,
-                                     const FrameIndex* fi, const BlockRef* blocks, const Piece* pieces,
-                                     const Chain* chains, PieceOut* outs, uint32_t* ticket, uint32_t hist);
+__global__ void decode_chains_kernel(const uint8_t* src, uint64_t n_src, uint8_t* dst, uint64_t dst_cap, uint32_t mode,
+                                     FrameIndex* fi, BlockRef* blocks, Piece* pieces, Chain* chains, uint32_t cap_tables,
+                                     uint32_t* stored_list, PieceOut* outs, uint32_t* ticket, uint32_t* walk, uint32_t hist);
 __global__ void decode_finalize_kernel(const FrameIndex* fi, const Piece* pieces, const PieceOut* outs,
                                        const uint32_t* block_crc_bad, DecodeResult* res, uint32_t* ticket);
 __global__ void verify_block_checksums_kernel(const uint8_t* src, const FrameIndex* fi,
