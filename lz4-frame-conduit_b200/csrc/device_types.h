@@ -76,8 +76,9 @@ struct DecodeResult {
 struct EncParams {
     uint64_t n;               // uncompressed bytes in this call
     uint32_t block_size;
-    uint32_t sub_size;        // independent sub-block size (divides block_size)
+    uint32_t sub_size;        // encoder unit: parsed by one warp, stitched by layout/gather (divides block_size)
     uint32_t subs_per_block;
+    uint32_t dom_units;       // units per match domain (= the independent sub-block one decoder warp decodes; index entries)
     uint32_t n_blocks;
     uint32_t n_subs;          // total sub-blocks
     uint32_t scratch_stride;  // bytes of scratch per sub-block

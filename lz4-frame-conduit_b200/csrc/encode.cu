@@ -37,6 +37,10 @@ __device__ __forceinline__ uint32_t put_len_ext(uint8_t* out, uint32_t o, uint32
     return o + n255 + 1u;
 }
 
+#ifndef B2_ENC_PRIME_STRIDE
+#define B2_ENC_PRIME_STRIDE 4
+#endif
+constexpr uint32_t ENC_PRIME_STRIDE = B2_ENC_PRIME_STRIDE;   // priming inserts every n-th earlier position of the domain
 constexpr uint32_t ENC_PREMEASURE = 28u;                  // matches are measured lane-parallel up to this length
 constexpr uint32_t NX_LONG = 254u, NX_NONE = 255u;     // link values: match end unknown yet / no further hit
 
@@ -142,16 +146,33 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
         const uint32_t blk = s / P.subs_per_block, j = s - blk * P.subs_per_block;
         const uint64_t blk_start = (uint64_t)blk * P.block_size;
         const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
+        // the warp parses the unit [b0, b1); its matches may reach back to d0, the start of the match domain the unit
+        // belongs to (dom_units units = the piece ONE decoder warp decodes, so nothing may reach before it)
         const uint32_t b0 = j * P.sub_size;
         const uint32_t b1 = (b0 + P.sub_size < usize) ? b0 + P.sub_size : usize;
+        const uint32_t d0 = (j / P.dom_units) * P.dom_units * P.sub_size;
         const bool last_sub = (b1 == usize);
         const uint8_t* __restrict__ base = src + blk_start;
         uint8_t* out = scratch + (uint64_t)s * P.scratch_stride;
 
-        // zero the table so the parse is deterministic
+        // zero the table so the parse is deterministic, then prime it with the part of the domain in front of the unit:
+        // every earlier position (at most 65535 back) is inserted, the later one winning — what a serial parse of the
+        // domain would have left there, only denser.  That is what lets the units of one domain be parsed by different
+        // warps at the same time without paying for it in ratio (tools/enc_model.c: SEG / PRIME).
         { uint4 z = make_uint4(0, 0, 0, 0); uint4* t4 = (uint4*)tab;
           for (uint32_t i = lane; i < HSIZE * 2 / 16; i += 32) t4[i] = z; }
         __syncwarp();
+        if (b0 > d0) {
+            const uint32_t from = (b0 - d0 > 65535u) ? b0 - 65535u : d0;
+            for (uint32_t q = from; q < b0; q += 128u * ENC_PRIME_STRIDE) {
+                #pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t pp = q + (32u * k + lane) * ENC_PRIME_STRIDE;
+                    if (pp < b0) TAB_ST(tab + hash4(ld32u(base + pp)), (uint16_t)(pp - d0));
+                }
+                __syncwarp();
+            }
+        }
 
         // positions that may start a match: p + 4 <= b1 and p <= usize - 12 (block end rule)
         uint32_t limit = 0;
@@ -177,7 +198,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
             for (int k = 0; k < 4; ++k) {
                 const uint32_t p = T0 + ((32u * k + lane) << sl);
                 ok[k] = p < limit;
-                rel[k] = p - b0;
+                rel[k] = p - d0;
                 v[k] = ok[k] ? ld32u(base + p) : 0u;
                 h[k] = hash4(v[k]);
             }
@@ -197,8 +218,8 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 bool hit = false;
                 pk[k] = 0;
                 if (c[k] >= 0) {
-                    const uint8_t* cp = base + b0 + c[k];
-                    const uint8_t* pp = base + b0 + rel[k];
+                    const uint8_t* cp = base + d0 + c[k];
+                    const uint8_t* pp = base + d0 + rel[k];
                     const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
                     const uint32_t* pw = (const uint32_t*)((uintptr_t)pp & ~(uintptr_t)3);
                     const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
@@ -211,7 +232,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                         const uint32_t x2 = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, psh);
                         const uint32_t x3 = __funnelshift_r(c2, c3, csh) ^ __funnelshift_r(p2, p3, psh);
                         uint32_t fl = 4u + (x2 ? ((uint32_t)(__ffs(x2) - 1) >> 3) : 4u + (x3 ? ((uint32_t)(__ffs(x3) - 1) >> 3) : 4u));
-                        const uint32_t room = matchlimit - (b0 + rel[k]);     // >= 7 for every probed position
+                        const uint32_t room = matchlimit - (d0 + rel[k]);     // >= 7 for every probed position
                         if (fl > room) fl = room;
                         uint32_t bk = 0;
                         if (bk_ok) {
@@ -235,10 +256,10 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                         todo &= todo - 1u;
                         const uint32_t pv = k == 0 ? pk[0] : k == 1 ? pk[1] : k == 2 ? pk[2] : pk[3];
                         const uint32_t rl = k == 0 ? rel[0] : k == 1 ? rel[1] : k == 2 ? rel[2] : rel[3];
-                        const uint32_t room = matchlimit - (b0 + rl);
+                        const uint32_t room = matchlimit - (d0 + rl);
                         if (room > 12u) {
-                            const uint8_t* cp = base + b0 + (pv & 0x3FFFFFu) + 12u;
-                            const uint8_t* pp = base + b0 + rl + 12u;
+                            const uint8_t* cp = base + d0 + (pv & 0x3FFFFFu) + 12u;
+                            const uint8_t* pp = base + d0 + rl + 12u;
                             const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
                             const uint32_t* pw = (const uint32_t*)((uintptr_t)pp & ~(uintptr_t)3);
                             const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
@@ -308,7 +329,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                         // the last match taken is 12+ bytes: measure it with the whole warp (4 bytes per lane per round;
                         // bytes at and after matchlimit never count)
                         const uint32_t lp = __shfl_sync(FULL_MASK, pos, npend - 1u);
-                        const uint32_t lc = b0 + (__shfl_sync(FULL_MASK, pkv, npend - 1u) & 0x3FFFFFu);
+                        const uint32_t lc = d0 + (__shfl_sync(FULL_MASK, pkv, npend - 1u) & 0x3FFFFFu);
                         uint32_t len = ENC_PREMEASURE;
                         for (uint32_t round = 0;; ++round) {
                             uint32_t nbytes = 0, per;
@@ -354,7 +375,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                         uint32_t back = pkv >> 27;
                         if (back > pos - prev_end) back = pos - prev_end;
                         const uint32_t mpos = pos - back;
-                        pd.anchor = prev_end; pd.ll = mpos - prev_end; pd.off = pos - (b0 + (pkv & 0x3FFFFFu)); pd.mlc = fl + back - 4u;
+                        pd.anchor = prev_end; pd.ll = mpos - prev_end; pd.off = pos - (d0 + (pkv & 0x3FFFFFu)); pd.mlc = fl + back - 4u;
                         // sample indices strictly inside the match: ((mpos - T0) >> sl) + 1 .. first index at or after mend
                         j0 = mpos >= T0 ? ((mpos - T0) >> sl) + 1u : 0u;
                         j1 = (mend - T0 + (1u << sl) - 1u) >> sl;
@@ -436,7 +457,7 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
         const uint64_t blk_start = (uint64_t)b * P.block_size;
         const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
         const uint32_t ns = (usize + P.sub_size - 1u) / P.sub_size;
-        uint32_t carry = 0, off = 0, nc = 0;
+        uint32_t carry = 0, off = 0, nc = 0, last_dom = 0xFFFFFFFFu;
         for (uint32_t j = 0; j < ns; ++j) {
             const uint32_t s = b * P.subs_per_block + j;
             const SubOut so = subs[s];
@@ -445,7 +466,8 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
                 uint32_t ll2 = so.first_ll + carry;
                 sp.new_hdr = 1u + len_bytes(ll2);
                 sp.size = so.out_len - so.first_hdr + sp.new_hdr + carry;
-                off += sp.size; carry = so.tail; ++nc;
+                off += sp.size; carry = so.tail;
+                if (j / P.dom_units != last_dom) { ++nc; last_dom = j / P.dom_units; }   // a decoder entry point per domain
             } else carry += so.tail;
             places[s] = sp;
         }
@@ -516,9 +538,11 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
             if (bp.stored) { st_le32(ce, 0u); st_le32(ce + 4, 0u); }
             else {
                 const uint32_t ns = (bp.usize + P.sub_size - 1u) / P.sub_size;
+                uint32_t last_dom = 0xFFFFFFFFu;
                 for (uint32_t j = 0; j < ns; ++j) {
                     const uint32_t s = b * P.subs_per_block + j;
-                    if (!subs[s].emitted) continue;
+                    if (j / P.dom_units == last_dom || !subs[s].emitted) continue;     // first emitting unit of every domain
+                    last_dom = j / P.dom_units;
                     const SubPlace sp = places[s];
                     st_le32(ce, sp.dst_rel); st_le32(ce + 4, j * P.sub_size - sp.carry_in);
                     ce += sizeof(IndexChain);

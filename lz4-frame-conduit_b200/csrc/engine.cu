@@ -277,7 +277,9 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     P.n = n;
     fill_desc(pr, P.desc, n);
     P.block_size = block_size_of(P.desc.block_size_id);
-    P.sub_size = sub_size_of(pr, P.block_size);
+    const uint32_t dom = sub_size_of(pr, P.block_size);             // match domain = what one decoder warp decodes
+    P.sub_size = std::min<uint32_t>(dom, ENC_UNIT);                 // encoder unit
+    P.dom_units = dom / P.sub_size;
     P.subs_per_block = P.block_size / P.sub_size;
     uint64_t nb = (n + P.block_size - 1) / P.block_size;
     if (nb > 0x7FFFFFFFull / P.subs_per_block) return err_code(E_srcSize_tooLarge);

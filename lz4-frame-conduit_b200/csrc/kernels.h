@@ -26,6 +26,10 @@ constexpr int ENC_CTAS_PER_SM = B2_ENC_CTAS;   // resident CTAs per SM the kerne
 #define B2_ENC_HLOG 13
 #endif
 constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 8192-entry u16 hash table per warp (16 KB)
+#ifndef B2_ENC_UNIT_LOG2
+#define B2_ENC_UNIT_LOG2 15
+#endif
+constexpr uint32_t ENC_UNIT = 1u << B2_ENC_UNIT_LOG2;   // bytes one match-finder warp parses at a time (a domain = sub-block holds several)
 constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
                   SCAN_LEGACY = 8u,

@@ -9,17 +9,22 @@ void b2gen_loglike(uint8_t*, size_t, uint64_t);
 static inline uint32_t rd32(const uint8_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
 static uint32_t lenb(uint32_t v) { return v >= 15 ? (v - 15) / 255 + 1 : 0; }
 int HLOG = 13, VARIANT = 0;
+unsigned SEG = 0, PRIME = 1;   /* SEG: encoder parse unit inside a sub-block (0 = whole sub-block); PRIME: 1 = insert every earlier position, 2/4 = every 2nd/4th, 9 = literal-ish heuristic */
 static uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - HLOG); }
 
 /* returns compressed size of sub-block [b0,b1) of block `base` (usize bytes); *tail = carried literals */
-static size_t sub(const uint8_t* base, uint32_t usize, uint32_t b0, uint32_t b1, int last, uint32_t carry, uint32_t* tail, size_t* nseq)
-{
+static size_t sub(const uint8_t* base, uint32_t usize, uint32_t b0, uint32_t b1x, int last, uint32_t carry, uint32_t* tail, size_t* nseq, uint32_t s0, uint32_t b1)
+{ (void)b1x;
     static uint16_t tab[1 << 16];
     memset(tab, 0, sizeof(uint16_t) << HLOG);
+    if (s0 > b0) {   /* prime the table with the history of this sub-block */
+        uint32_t from = s0 - b0 > 65535 ? s0 - 65535 : b0;
+        for (uint32_t p = from; p < s0; p += PRIME) tab[hash4(rd32(base + p))] = (uint16_t)(p - b0);
+    }
     uint32_t limit = 0;
     if (usize >= 13) { uint32_t la = b1 >= 3 ? b1 - 3 : 0, lb = usize - 11; limit = la < lb ? la : lb; }
     uint32_t matchlimit = usize >= 5 ? (b1 < usize - 5 ? b1 : usize - 5) : 0;
-    uint32_t ip = b0, anchor = b0, miss = 0; size_t o = 0; int first = 1;
+    uint32_t ip = s0, anchor = s0, miss = 0; size_t o = 0; int first = 1;
     while (ip < limit) {
         uint32_t sl = (miss >> 2) < 3 ? (miss >> 2) : 3;
         int f = -1; uint32_t cf = 0;
@@ -60,6 +65,8 @@ int main(int argc, char** argv) {
     HLOG = argc > 2 ? atoi(argv[2]) : 13;
     uint32_t S = 1u << (argc > 3 ? atoi(argv[3]) : 18);
     VARIANT = argc > 4 ? atoi(argv[4]) : 0;
+    if (getenv("SEG")) SEG = (unsigned)atoi(getenv("SEG"));
+    if (getenv("PRIME")) PRIME = (unsigned)atoi(getenv("PRIME"));
     uint8_t* d = malloc(n);
     if (argc > 5) { FILE* f = fopen(argv[5], "rb"); n = fread(d, 1, n, f); fclose(f); }
     else b2gen_loglike(d, n, 0x10C5);
@@ -69,7 +76,11 @@ int main(int argc, char** argv) {
         uint32_t usize = (uint32_t)(n - b < BS ? n - b : BS), carry = 0; size_t c = 0;
         for (uint32_t b0 = 0; b0 < usize; b0 += S) {
             uint32_t b1 = b0 + S < usize ? b0 + S : usize;
-            c += sub(d + b, usize, b0, b1, b1 == usize, carry, &carry, &nseq);
+            uint32_t seg = SEG ? SEG : S;
+            for (uint32_t s0 = b0; s0 < b1; s0 += seg) {
+                uint32_t s1 = s0 + seg < b1 ? s0 + seg : b1;
+                c += sub(d + b, usize, b0, b1, s1 == usize, carry, &carry, &nseq, s0, s1);
+            }
         }
         total += 4 + (c >= usize ? usize : c);
     }
