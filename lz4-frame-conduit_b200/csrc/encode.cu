@@ -41,6 +41,7 @@ __device__ __forceinline__ uint32_t put_len_ext(uint8_t* out, uint32_t o, uint32
 #define B2_ENC_PRIME_STRIDE 4
 #endif
 constexpr uint32_t ENC_PRIME_STRIDE = B2_ENC_PRIME_STRIDE;   // priming inserts every n-th earlier position of the domain
+constexpr uint32_t ENC_PRIME_NEAR = 4096u;                   // history primed before the unit is known to be compressible
 constexpr uint32_t ENC_PREMEASURE = 28u;                  // matches are measured lane-parallel up to this length
 constexpr uint32_t NX_LONG = 254u, NX_NONE = 255u;     // link values: match end unknown yet / no further hit
 
@@ -163,14 +164,44 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
           for (uint32_t i = lane; i < HSIZE * 2 / 16; i += 32) t4[i] = z; }
         __syncwarp();
         if (b0 > d0) {
+            // priming 64 KB costs more than parsing a unit of incompressible data, so it is done in two steps: the newest
+            // 4 KB first; if none of the unit's first 256 positions finds a match there, the unit is taken to be
+            // incompressible and parsed with that much history only (its own matches are still found)
             const uint32_t from = (b0 - d0 > 65535u) ? b0 - 65535u : d0;
-            for (uint32_t q = from; q < b0; q += 128u * ENC_PRIME_STRIDE) {
-                #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t pp = q + (32u * k + lane) * ENC_PRIME_STRIDE;
-                    if (pp < b0) TAB_ST(tab + hash4(ld32u(base + pp)), (uint16_t)(pp - d0));
+            const uint32_t near = (b0 - from > ENC_PRIME_NEAR) ? b0 - ENC_PRIME_NEAR : from;
+            auto prime = [&](uint32_t lo) {
+                for (uint32_t q = lo; q < b0; q += 128u * ENC_PRIME_STRIDE) {
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t pp = q + (32u * k + lane) * ENC_PRIME_STRIDE;
+                        const uint32_t vv = pp < b0 ? ld32u(base + pp) : 0u;
+                        // inside a run the neighbouring position has the same hash: only the later one needs the slot
+                        const uint32_t vn = __shfl_down_sync(FULL_MASK, vv, 1);
+                        if (pp < b0 && (lane == 31u || vn != vv || pp + ENC_PRIME_STRIDE >= b0)) TAB_ST(tab + hash4(vv), (uint16_t)(pp - d0));
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
+            };
+            prime(near);
+            if (near > from) {
+                bool hit = false;
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t pp = b0 + 32u * k + lane;
+                    if (pp + 4u <= b1) {
+                        const uint32_t vv = ld32u(base + pp);
+                        const uint32_t cl = TAB_LD(tab + hash4(vv));
+                        int32_t cc = (int32_t)(((pp - d0) & ~0xFFFFu) | cl);
+                        if ((uint32_t)cc >= pp - d0) cc -= 65536;
+                        if (cc >= 0 && ld32u(base + d0 + cc) == vv) hit = true;
+                    }
+                }
+                if (__any_sync(FULL_MASK, hit)) {                           // compressible: the whole history, oldest first
+                    { uint4 z = make_uint4(0, 0, 0, 0); uint4* t4 = (uint4*)tab;
+                      for (uint32_t i = lane; i < HSIZE * 2 / 16; i += 32) t4[i] = z; }
+                    __syncwarp();
+                    prime(from);
+                }
             }
         }
 
