@@ -490,6 +490,15 @@ static size_t pipe_chunk(const b2lz4_ctx* ctx, size_t n, size_t block_size) {
     c = std::max(block_size, c / block_size * block_size);
     return c;
 }
+// Chunk plan of a host-buffer call: start offsets in `unit`s, the last entry being the total.  Uniform chunks of `base`
+// units (a plan that starts and ends with quarter / half chunks was measured and bought nothing: 26.0 vs 26.0 ms per GiB).
+static std::vector<size_t> plan_chunks(const b2lz4_ctx* ctx, size_t total, size_t base) {
+    (void)ctx;
+    std::vector<size_t> v{0};
+    base = std::max<size_t>(1, base);
+    for (size_t at = 0; at < total;) v.push_back(at = std::min(total, at + base));
+    return v;
+}
 static bool multi_dev(const b2lz4_ctx* ctx) { return ctx->n_devs > 1; }
 static int lane_device(const b2lz4_ctx* ctx, int k) { return ctx->n_devs > 0 ? ctx->devs[k % ctx->n_devs] : ctx->device; }
 static size_t ensure_lanes(b2lz4_ctx* ctx, int want) {
@@ -561,7 +570,8 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     if (!whole) pr.write_index = 0;
     const size_t bs = block_size_of(pr.block_size_id ? pr.block_size_id : 7u);
     const size_t chunk = pipe_chunk(ctx, n, bs);
-    const size_t nchunks = n ? (n + chunk - 1) / chunk : 0;
+    const std::vector<size_t> plan = plan_chunks(ctx, (n + bs - 1) / bs, chunk / bs);      // in blocks
+    const size_t nchunks = plan.size() - 1;
     const int L = (int)std::min<size_t>((size_t)pipe_lanes(ctx), std::max<size_t>(1, nchunks));
     r = ensure_lanes(ctx, L); if (r) return r;
     uint8_t* out = (uint8_t*)dst;
@@ -591,7 +601,7 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
 
     auto submit = [&](size_t i) -> size_t {
         b2lz4_ctx* ln = ctx->lanes[i % L];
-        const size_t off = i * chunk, len = std::min(chunk, n - off);
+        const size_t off = plan[i] * bs, len = std::min(plan[i + 1] * bs, n) - off;
         LANE_CU(ln, cudaSetDevice(ln->device));
         LANE_CU(ln, ln->stage_in.ensure(len + 16));
         LANE_CU(ln, ln->stage_out.ensure(b2lz4_compress_bound(len, &pr) + 16));
@@ -610,7 +620,7 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     };
     auto complete = [&](size_t i) -> size_t {
         b2lz4_ctx* ln = ctx->lanes[i % L];
-        const size_t off = i * chunk, len = std::min(chunk, n - off);
+        const size_t off = plan[i] * bs, len = std::min(plan[i + 1] * bs, n) - off;
         LANE_CU(ln, cudaSetDevice(ln->device));
         size_t c = compress_finish(ln, len);                                    // waits for the lane
         if (b2lz4_is_error(c)) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return c; }
@@ -772,7 +782,9 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
     size_t r = 0;
     const bool whole = hmode == HOSTC_FRAME;
     ctx->stats = b2lz4_stats{};
-    const size_t nb = f.blocks.size(), ngroups = (nb + per_group - 1) / per_group;
+    const size_t nb = f.blocks.size();
+    const std::vector<size_t> plan = plan_chunks(ctx, nb, per_group);
+    const size_t ngroups = plan.size() - 1;
     const int L = (int)std::min<size_t>((size_t)pipe_lanes(ctx), ngroups);
     r = ensure_lanes(ctx, L); if (r) return r;
     const uint32_t bc = f.desc.block_checksum ? 4u : 0u;
@@ -789,7 +801,7 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
 
     auto submit = [&](size_t g) -> size_t {
         b2lz4_ctx* ln = ctx->lanes[g % L];
-        const size_t b0 = g * per_group, b1 = std::min(nb, b0 + per_group);
+        const size_t b0 = plan[g], b1 = plan[g + 1];
         const size_t s0 = f.blocks[b0].off, s1 = b1 < nb ? f.blocks[b1].off : f.end_blocks;
         (void)bc;
         // the group's slice of the index, rebased: [skip magic, size][IndexHead][blocks][chains][size, magic]
