@@ -9,7 +9,7 @@ void b2gen_loglike(uint8_t*, size_t, uint64_t);
 static inline uint32_t rd32(const uint8_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
 static uint32_t lenb(uint32_t v) { return v >= 15 ? (v - 15) / 255 + 1 : 0; }
 int HLOG = 13, VARIANT = 0;
-unsigned SEG = 0, PRIME = 1;   /* SEG: encoder parse unit inside a sub-block (0 = whole sub-block); PRIME: 1 = insert every earlier position, 2/4 = every 2nd/4th, 9 = literal-ish heuristic */
+unsigned SEG = 0, PRIME = 1, MINLEN = 4, LAZY = 0;   /* SEG: encoder parse unit inside a sub-block (0 = whole sub-block); PRIME: 1 = insert every earlier position, 2/4 = every 2nd/4th, 9 = literal-ish heuristic */
 static uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - HLOG); }
 
 /* returns compressed size of sub-block [b0,b1) of block `base` (usize bytes); *tail = carried literals */
@@ -47,7 +47,21 @@ static size_t sub(const uint8_t* base, uint32_t usize, uint32_t b0, uint32_t b1x
         while (mpos > anchor && cpos > b0 && base[mpos - 1] == base[cpos - 1]) { --mpos; --cpos; }
         uint32_t len = 0;
         while (mpos + len < matchlimit && base[mpos + len] == base[cpos + len]) ++len;
-        if (len < 4) { ip = mpos + 1; continue; }
+        if (len < MINLEN) { ip = mpos + 1; continue; }
+        if (LAZY && len < LAZY) {
+            int better = 0;
+            uint32_t p0 = ip + ((uint32_t)f << sl);
+            for (uint32_t d = 1; d <= 3 && !better; ++d) {
+                uint32_t p = p0 + d; if (p >= limit) break;
+                uint32_t v = rd32(base + p), rel = p - b0;
+                int32_t c = (int32_t)((rel & ~0xFFFFu) | tab[hash4(v)]); if ((uint32_t)c >= rel) c -= 65536;
+                if (c >= 0 && rel - (uint32_t)c < 65536 && rd32(base + b0 + c) == v) {
+                    uint32_t l2 = 0; while (p + l2 < matchlimit && base[p + l2] == base[b0 + c + l2]) ++l2;
+                    if (l2 >= len + 2) better = 1;
+                }
+            }
+            if (better) { ip = p0 + 1; continue; }
+        }
         uint32_t ll = mpos - anchor + (first ? carry : 0); first = 0;
         o += 1 + lenb(ll) + ll + 2 + lenb(len - 4); ++*nseq;
         ip = mpos + len; anchor = ip;
@@ -67,6 +81,8 @@ int main(int argc, char** argv) {
     VARIANT = argc > 4 ? atoi(argv[4]) : 0;
     if (getenv("SEG")) SEG = (unsigned)atoi(getenv("SEG"));
     if (getenv("PRIME")) PRIME = (unsigned)atoi(getenv("PRIME"));
+    if (getenv("LAZY")) LAZY = (unsigned)atoi(getenv("LAZY"));
+    if (getenv("MINLEN")) MINLEN = (unsigned)atoi(getenv("MINLEN"));
     uint8_t* d = malloc(n);
     if (argc > 5) { FILE* f = fopen(argv[5], "rb"); n = fread(d, 1, n, f); fclose(f); }
     else b2gen_loglike(d, n, 0x10C5);
