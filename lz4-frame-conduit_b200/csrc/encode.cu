@@ -6,7 +6,7 @@
 //   LZ4F_makeBlock (block header word, stored-block fallback)         lz4/lib/lz4frame.c:739-761
 //   LZ4F_compressBegin / LZ4F_compressEnd (header, EndMark)           lz4frame.c:600-702, 984-1018
 // This is NOT a port of that code: the reference walks one position at a time with a 4 K-entry table;
-// here one warp probes 32 positions per step against an 8 K-entry shared-memory table, a 4 MB frame
+// here one warp probes 128 positions per step against a 4 K-entry shared-memory table, a 4 MB frame
 // block is cut into independent sub-blocks (one warp each) whose outputs are stitched by prefix sums,
 // and the only things kept from the reference are the *format rules* every LZ4 encoder must obey
 // (lz4_Block_format.md:108-129: last 5 bytes literal, last match starts >= 12 bytes before the end,
@@ -46,7 +46,7 @@ constexpr uint32_t ENC_PRIME_STRIDE = B2_ENC_PRIME_STRIDE;   // priming inserts 
 #endif
 constexpr uint32_t ENC_MINLEN = B2_ENC_MINLEN;               // matches shorter than this (forward + backward bytes seen at verify time) are ignored
 #ifndef B2_ENC_LAZY
-#define B2_ENC_LAZY 16
+#define B2_ENC_LAZY 24
 #endif
 constexpr uint32_t ENC_LAZY = B2_ENC_LAZY;                   // matches shorter than this give way to a longer one 1..3 positions later (0 = off)
 constexpr uint32_t ENC_PRIME_NEAR = 4096u;                   // history primed before the unit is known to be compressible

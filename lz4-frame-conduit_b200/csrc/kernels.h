@@ -14,7 +14,7 @@ constexpr int DEC_WARPS = B2_DEC_WARPS;          // warps per CTA in the sequenc
 #define B2_ENC_WARPS 8
 #endif
 #ifndef B2_ENC_SMEM_WARPS
-#define B2_ENC_SMEM_WARPS 2
+#define B2_ENC_SMEM_WARPS 6
 #endif
 #ifndef B2_ENC_CTAS
 #define B2_ENC_CTAS 4
@@ -23,11 +23,11 @@ constexpr int ENC_WARPS = B2_ENC_WARPS;          // warps per CTA in the match f
 constexpr int ENC_SMEM_WARPS = B2_ENC_SMEM_WARPS;     // ... of which this many keep their table in shared memory; the others use a global (L1/L2) table
 constexpr int ENC_CTAS_PER_SM = B2_ENC_CTAS;   // resident CTAs per SM the kernel is built for
 #ifndef B2_ENC_HLOG
-#define B2_ENC_HLOG 13
+#define B2_ENC_HLOG 12
 #endif
-constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 8192-entry u16 hash table per warp (16 KB)
+constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 4096-entry u16 hash table per warp (8 KB), the reference's table size for large inputs
 #ifndef B2_ENC_UNIT_LOG2
-#define B2_ENC_UNIT_LOG2 15
+#define B2_ENC_UNIT_LOG2 14
 #endif
 constexpr uint32_t ENC_UNIT = 1u << B2_ENC_UNIT_LOG2;   // bytes one match-finder warp parses at a time (a domain = sub-block holds several)
 constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
