@@ -21,6 +21,9 @@ __global__ void xxh32_reset_kernel(XxhState* st) {
     }
 }
 
+#ifndef B2_XXH_CHAIN
+#define B2_XXH_CHAIN 1
+#endif
 // XXH32_update over data[0, n) (xxhash.c:452-526).  Launch with ONE CTA of 256 threads.
 __global__ void __launch_bounds__(256)
 xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t* __restrict__ n_ptr,
@@ -79,8 +82,27 @@ xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t
                 uint32_t x[8];
                 #pragma unroll
                 for (int k = 0; k < 8; ++k) x[k] = w[4u * (i + k)];
+#if B2_XXH_CHAIN == 0
                 #pragma unroll
                 for (int k = 0; k < 8; ++k) acc = xxh32_round(acc, x[k]);
+#else
+                // round(acc, w) = rotl13(acc + w*P2) * P1.  With X = acc + w*P2:  rotl13(X) = (X << 13) + (X >> 19) (disjoint
+                // bits), so round = X*(P1 << 13) + (X >> 19)*P1, and the NEXT X is (X >> 19)*P1 + [X*(P1 << 13) + w'*P2]:
+                // the bracket does not wait for the shift, which leaves two dependent instructions per stripe instead of three
+                // (measured on B200: 1.97 -> 2.44 GB/s for one stream).
+                constexpr uint32_t P1 = 2654435761u, P2 = 2246822519u, K1 = P1 << 13;
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] *= P2;
+                uint32_t X = acc + x[0];
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t t = X >> 19;                               // (__umulhi(X, 1 << 13) on the multiplier pipe: 1.36 GB/s)
+                    uint32_t u;                                                // inline PTX: nvcc re-associates the C form into a 3-deep chain
+                    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(u) : "r"(X), "r"(K1), "r"(k < 7 ? x[k < 7 ? k + 1 : 7] : 0u));
+                    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(X) : "r"(t), "r"(P1), "r"(u));
+                }
+                acc = X;
+#endif
             }
             for (; i < ns; ++i) acc = xxh32_round(acc, w[4u * i]);
         }

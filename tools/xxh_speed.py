@@ -5,6 +5,7 @@ import torch, ctypes as C
 pkg = importlib.import_module("lz4-frame-conduit_b200")
 c = pkg.Codec(0)
 n = 1 << 30
+torch.manual_seed(1)
 d = torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda")
 h = C.c_uint32(0)
 c.lib.b2lz4_xxh32_device(c.h, C.c_void_p(d.data_ptr()), C.c_size_t(n), C.byref(h)); torch.cuda.synchronize()
