@@ -6,8 +6,10 @@
 //   LZ4F_makeBlock (block header word, stored-block fallback)         lz4/lib/lz4frame.c:739-761
 //   LZ4F_compressBegin / LZ4F_compressEnd (header, EndMark)           lz4frame.c:600-702, 984-1018
 // This is NOT a port of that code: the reference walks one position at a time with a 4 K-entry table;
-// here one warp probes 128 positions per step against a 4 K-entry shared-memory table, a 4 MB frame
-// block is cut into independent sub-blocks (one warp each) whose outputs are stitched by prefix sums,
+// here one warp probes 128 positions per step against a 4 K-entry shared-memory table and weighs the
+// 128 measured matches against each other (lazy evaluation) before it picks, a 4 MB frame block is cut
+// into independent sub-blocks (match domains) parsed by several warps at once, 16 KB each, whose outputs
+// are stitched by prefix sums,
 // and the only things kept from the reference are the *format rules* every LZ4 encoder must obey
 // (lz4_Block_format.md:108-129: last 5 bytes literal, last match starts >= 12 bytes before the end,
 // inputs < 13 bytes are literal-only, offsets <= 65535) and the stored-block rule of the frame layer
@@ -123,8 +125,8 @@ __device__ __forceinline__ uint32_t emit_batch(uint8_t* __restrict__ out, uint32
 //              is parked in a lane (Pending) and written out 32 at a time (emit_batch)
 //   4. insert  positions that did not end up inside a match go into the table (inserting match
 //              interiors would evict the field starts the following lines need)
-// After a step without a hit the probe stride doubles (1, 2, 4, 8 bytes), as incompressible data should
-// cost little; a hit resets it.
+// After a step without a hit the probe stride doubles (1, 2, 4, 8 bytes; 16 and 32 after 8 and 16 empty steps),
+// as incompressible data should cost little; a hit resets it.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(ENC_WARPS * 32, ENC_CTAS_PER_SM)
 find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restrict__ scratch,
@@ -132,9 +134,9 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 {
     extern __shared__ __align__(16) uint16_t s_tab[];
     const uint32_t lane = lane_id();
-    // half of the CTA's warps keep their hash table in shared memory, the other half in a global table that
-    // lives in L1/L2: twice the warps per SM for the same shared memory, and the extra look-up latency is
-    // small next to the candidate fetches every step already waits for
+    // ENC_SMEM_WARPS (6 of 8) warps keep their hash table in shared memory, the others in a global table that
+    // lives in L1/L2: 32 warps per SM fit that way (192 KB of tables), and measured against 24 warps with every
+    // table in shared memory the occupancy wins (59 vs 55.5 GB/s)
     const uint32_t wid = threadIdx.x >> 5;
     uint16_t* tab = wid < (uint32_t)ENC_SMEM_WARPS ? s_tab + wid * HSIZE
                   : gtab + ((size_t)blockIdx.x * (ENC_WARPS - ENC_SMEM_WARPS) + (wid - ENC_SMEM_WARPS)) * HSIZE;
@@ -165,7 +167,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
         uint8_t* out = scratch + (uint64_t)s * P.scratch_stride;
 
         // zero the table so the parse is deterministic, then prime it with the part of the domain in front of the unit:
-        // every earlier position (at most 65535 back) is inserted, the later one winning — what a serial parse of the
+        // every ENC_PRIME_STRIDE-th earlier position (at most 65535 back) is inserted, the later one winning — what a serial parse of the
         // domain would have left there, only denser.  That is what lets the units of one domain be parsed by different
         // warps at the same time without paying for it in ratio (tools/enc_model.c: SEG / PRIME).
         { uint4 z = make_uint4(0, 0, 0, 0); uint4* t4 = (uint4*)tab;
