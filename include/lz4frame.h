@@ -26,7 +26,8 @@
  *   - free(NULL) is a no-op; contexts are not thread-safe, distinct contexts are independent.
  * What differs (allowed by the format, lz4_Frame_format.md): frames are always written with independent
  * blocks, LZ4F_default block size means 256 KB, and the encoder works in batches (B2LZ4_BATCH_MB, default
- * 64 MiB), so LZ4F_compressBound() is larger than the reference's and output arrives in larger pieces.
+ * 32 MiB, one on the GPU while the next is staged), so LZ4F_compressBound() is larger than the reference's
+ * and output arrives in larger pieces, one batch late.
  * There is no CPU codec behind these symbols: without a usable CUDA device they return ERROR_cudaFailure.
  */
 #ifndef B200_LZ4FRAME_H

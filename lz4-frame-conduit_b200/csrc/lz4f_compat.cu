@@ -12,6 +12,10 @@
 #include <string.h>
 #include <new>
 #include <algorithm>
+#include <chrono>
+#include <future>
+#include <mutex>
+#include <stdio.h>
 #include "format.h"
 #include "../../include/b200lz4.h"
 #include "../../include/lz4frame.h"
@@ -22,11 +26,12 @@ namespace {
 
 inline size_t ec(uint32_t e) { return (size_t)0 - (size_t)e; }
 
-size_t batch_bytes() {                       // B2LZ4_BATCH_MB: uncompressed bytes handed to the GPU per call (default 64 MiB)
+size_t batch_bytes() {                       // B2LZ4_BATCH_MB: uncompressed bytes handed to the GPU per call (default 32 MiB:
+                                             // the GPU is done with a batch before the host has copied the next one in)
     static size_t v = 0;
     if (!v) {
         const char* e = getenv("B2LZ4_BATCH_MB");
-        long mb = e ? atol(e) : 64;
+        long mb = e ? atol(e) : 32;
         if (mb < 4) mb = 4;
         if (mb > 2048) mb = 2048;
         v = ((size_t)mb << 20) & ~(((size_t)4 << 20) - 1);
@@ -48,24 +53,65 @@ size_t apply_devices(b2lz4_ctx* gpu) {
     return n ? b2lz4_set_devices(gpu, devs, n) : 0;
 }
 
+// B2LZ4_TRACE=1: every context prints, when it is freed, where its wall-clock time went (host copies in / GPU batches /
+// host copies out) — the Tier-1 layer is host-copy bound, this is how that was measured
+bool trace_on() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_TRACE"); v = (e && *e && *e != '0') ? 1 : 0; } return v == 1; }
+struct Trace {
+    double t_in = 0, t_gpu = 0, t_out = 0, t_all = 0; uint64_t calls = 0, batches = 0;
+    static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+    void report(const char* what) const {
+        if (trace_on()) fprintf(stderr, "[b2lz4 %s] calls %llu, batches %llu: inside the library %.3f s (copy-in %.3f, gpu %.3f, copy-out %.3f)\n", what,
+                                (unsigned long long)calls, (unsigned long long)batches, t_all, t_in, t_gpu, t_out);
+    }
+};
+struct Span { double& acc; double t0; explicit Span(double& a) : acc(a), t0(trace_on() ? Trace::now() : 0) {} ~Span() { if (trace_on()) acc += Trace::now() - t0; } };
+
+// Pinning host memory costs ~0.5 ms per MB (and unpinning as much), which is more than a short stream's whole GPU time and
+// erratic under virtualisation: staging buffers of finished contexts are kept in a small process-wide pool and handed to
+// the next context instead of going back to the driver (a program that runs one conduit after the other pins once).
+struct PinnedPool {
+    static constexpr int SLOTS = 12;
+    static constexpr size_t MAX_TOTAL = (size_t)768 << 20;
+    std::mutex mu; uint8_t* p[SLOTS] = {}; size_t cap[SLOTS] = {}; size_t total = 0;
+    uint8_t* get(size_t n, size_t* got) {                      // smallest pooled buffer that fits without wasting more than 4x
+        std::lock_guard<std::mutex> g(mu);
+        int best = -1;
+        for (int i = 0; i < SLOTS; ++i) if (p[i] && cap[i] >= n && cap[i] <= 4 * n + (1u << 20) && (best < 0 || cap[i] < cap[best])) best = i;
+        if (best < 0) return nullptr;
+        uint8_t* q = p[best]; *got = cap[best]; total -= cap[best]; p[best] = nullptr; cap[best] = 0;
+        return q;
+    }
+    bool put(uint8_t* q, size_t n) {
+        std::lock_guard<std::mutex> g(mu);
+        if (total + n > MAX_TOTAL) return false;
+        for (int i = 0; i < SLOTS; ++i) if (!p[i]) { p[i] = q; cap[i] = n; total += n; return true; }
+        return false;
+    }
+};
+PinnedPool& pinned_pool() { static PinnedPool* pool = new PinnedPool(); return *pool; }   // never destroyed: outlives CUDA teardown order
+
 struct Pinned {                              // growable pinned host buffer
     uint8_t* p = nullptr; size_t cap = 0;
-    bool ensure(size_t n, size_t keep = 0) {
+    // buffers of known size are allocated exactly, growing ones in few, large steps
+    bool ensure(size_t n, size_t keep = 0, bool exact = false) {
         if (n <= cap) return true;
-        uint8_t* q = (uint8_t*)b2lz4_pinned_alloc(n + n / 4 + 4096);
+        size_t want = exact ? n : 2 * n + 4096;
+        uint8_t* q = pinned_pool().get(n, &want);
+        if (!q) q = (uint8_t*)b2lz4_pinned_alloc(want);
         if (!q) return false;
         if (keep) memcpy(q, p, keep);
-        b2lz4_pinned_free(p);
-        p = q; cap = n + n / 4 + 4096;
+        release();
+        p = q; cap = want;
         return true;
     }
-    void release() { b2lz4_pinned_free(p); p = nullptr; cap = 0; }
+    void release() { if (p && !pinned_pool().put(p, cap)) b2lz4_pinned_free(p); p = nullptr; cap = 0; }
 };
 
 // LZ4F_default -> 256 KB blocks here, each parsed as ONE independent unit: such a frame needs no side information to be
 // decoded block-parallel (by this library's decoder as by any other), and its ratio on log-like data is 1 % better than
 // the reference's default (linked 64 KB blocks).  4 MB / 1 MB blocks stay available through blockSizeID.
 constexpr unsigned DEFAULT_BLOCK_ID = 5u;
+constexpr size_t HINT_MAX = (size_t)512 << 10;
 uint32_t block_bytes_of(unsigned id) { return block_size_of(id ? id : DEFAULT_BLOCK_ID); }
 
 // worst case bytes of the block region for n input bytes: every block stored + header word + checksum
@@ -81,10 +127,14 @@ struct LZ4F_cctx_s {
     uint32_t block_size = 0;
     size_t batch = 0;
     Pinned in;  size_t in_len = 0;
-    Pinned out;
+    Pinned in2, out;                                         // the batch in flight reads in2 and writes out
+    std::future<size_t> job; bool flight = false;            // at most one batch is on the GPU while the caller fills the next
     bool begun = false, first = true;
     uint64_t total_in = 0;
+    Trace tr;
 };
+
+static void drop_flight(LZ4F_cctx* c) { if (c->flight) { c->job.wait(); (void)c->job.get(); c->flight = false; } }
 
 extern "C" {
 
@@ -103,8 +153,13 @@ LZ4F_errorCode_t LZ4F_createCompressionContext(LZ4F_cctx** cctxPtr, unsigned ver
 
 LZ4F_errorCode_t LZ4F_freeCompressionContext(LZ4F_cctx* c) {
     if (!c) return 0;                                                    // lz4frame.c:554
+    drop_flight(c);
+    c->tr.report("cctx");
+    const double t0 = trace_on() ? Trace::now() : 0;
     b2lz4_destroy(c->gpu);
-    c->in.release(); c->out.release();
+    const double t1 = trace_on() ? Trace::now() : 0;
+    c->in.release(); c->out.release(); c->in2.release();
+    if (trace_on()) fprintf(stderr, "[b2lz4 cctx] free: engine context %.3f s, staging %.3f s\n", t1 - t0, Trace::now() - t1);
     delete c;
     return 0;
 }
@@ -118,13 +173,14 @@ size_t LZ4F_compressBound(size_t srcSize, const LZ4F_preferences_t* p) {
     const unsigned id = (unsigned)p->frameInfo.blockSizeID;
     if (id != 0 && (id < 4 || id > 7)) return ec(E_maxBlockSize_invalid);
     const uint32_t bs = block_bytes_of(id);
-    const size_t buffered = p->autoFlush ? 0 : batch_bytes() - 1;
+    const size_t buffered = p->autoFlush ? 0 : 2 * batch_bytes() - 1;            // one batch on the GPU, one being staged
     return blocks_bound(buffered + srcSize, bs, p->frameInfo.blockChecksumFlag != 0) + 8;
 }
 
 size_t LZ4F_compressBegin(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_preferences_t* p) {
     if (!c || !dst) return ec(E_GENERIC);
     if (cap < (size_t)LZ4F_HEADER_SIZE_MAX) return ec(E_dstMaxSize_tooSmall);       // lz4frame.c:613
+    drop_flight(c);                                                              // a frame abandoned without compressEnd
     LZ4F_preferences_t z; memset(&z, 0, sizeof z);
     c->prefs = p ? *p : z;
     const unsigned id = (unsigned)c->prefs.frameInfo.blockSizeID;
@@ -153,8 +209,36 @@ size_t LZ4F_compressBegin(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_prefer
 }
 
 // compresses the staged bytes [0, n) into dst; returns bytes written
+// the batch in flight has to finish; its blocks go to dst.  Returns bytes written.
+static size_t collect_flight(LZ4F_cctx* c, uint8_t* dst, size_t cap) {
+    if (!c->flight) return 0;
+    size_t r;
+    { Span sp(c->tr.t_gpu); r = c->job.get(); }
+    c->flight = false;
+    if (b2lz4_is_error(r)) return r;
+    if (r > cap) return ec(E_dstMaxSize_tooSmall);
+    { Span sp(c->tr.t_out); memcpy(dst, c->out.p, r); }
+    return r;
+}
+
+// hands the staged batch [0, n) to the GPU on a helper thread and makes the other staging buffer the one being filled:
+// the caller keeps copying input while the GPU compresses (this layer's time is host copies for the most part, B2LZ4_TRACE)
+static size_t launch_staged(LZ4F_cctx* c, size_t n) {
+    const size_t ocap = blocks_bound(n, c->block_size, c->bp.block_checksum != 0) + 16;
+    if (!c->out.ensure(ocap, 0, true) || !c->in2.ensure(c->batch + 16, 0, true)) return ec(E_allocation_failed);   // what the next batch needs
+    std::swap(c->in, c->in2);
+    ++c->tr.batches;
+    b2lz4_ctx* gpu = c->gpu; const uint8_t* src = c->in2.p; uint8_t* dst = c->out.p;
+    const unsigned flags = c->first ? B2LZ4_STREAM_FIRST : 0u;
+    c->job = std::async(std::launch::async, [=]() { return b2lz4_compress_blocks_host(gpu, src, n, dst, ocap, flags); });
+    c->flight = true; c->first = false;
+    return 0;
+}
+
+// compresses the staged bytes [0, n) into dst now (autoFlush, flush, end); returns bytes written
 static size_t emit_staged(LZ4F_cctx* c, size_t n, uint8_t* dst, size_t cap) {
     if (n == 0) return 0;
+    Span sp(c->tr.t_gpu); ++c->tr.batches;
     size_t r = b2lz4_compress_blocks_host(c->gpu, c->in.p, n, dst, cap, c->first ? B2LZ4_STREAM_FIRST : 0u);
     if (b2lz4_is_error(r)) return r;
     c->first = false;
@@ -166,9 +250,12 @@ size_t LZ4F_compressUpdate(LZ4F_cctx* c, void* dstBuffer, size_t cap, const void
     (void)opt;
     if (!c || !c->begun) return ec(E_GENERIC);                                       // lz4frame.c:836
     if (n && !src) return ec(E_srcPtr_wrong);
+    ++c->tr.calls;
+    Span whole(c->tr.t_all);
     uint8_t* dst = (uint8_t*)dstBuffer;
     const bool bc = c->bp.block_checksum != 0;
-    // bytes this call will push through the GPU: whole batches, or everything when autoFlush is set
+    // bytes this call may emit: a batch leaves when the NEXT one is full (it is compressed while that one is being
+    // staged), so whole batches as before; everything when autoFlush is set
     const size_t have = c->in_len + n;
     const size_t go = c->prefs.autoFlush ? have : (have / c->batch) * c->batch;
     if (cap < blocks_bound(go, c->block_size, bc)) return ec(E_dstMaxSize_tooSmall); // lz4frame.c:837-838
@@ -176,16 +263,23 @@ size_t LZ4F_compressUpdate(LZ4F_cctx* c, void* dstBuffer, size_t cap, const void
     const uint8_t* s = (const uint8_t*)src;
     size_t written = 0, left = n;
     const size_t stage_cap = c->prefs.autoFlush ? std::max(have, c->batch) : c->batch;
-    if (!c->in.ensure(stage_cap + 16, c->in_len)) return ec(E_allocation_failed);
+    {   // short streams should not pay for pinning a whole batch: the staging buffer grows with what has arrived
+        const size_t need_in = std::min(stage_cap, std::max<size_t>(have, (size_t)1 << 20));
+        const bool full = 2 * need_in >= stage_cap;
+        if (!c->in.ensure((full ? stage_cap : need_in) + 16, c->in_len, full)) return ec(E_allocation_failed);
+    }
     while (left) {
         const size_t room = stage_cap - c->in_len;
         const size_t take = left < room ? left : room;
-        memcpy(c->in.p + c->in_len, s, take);                                        // pinned staging (replaces tmpIn, lz4frame.c:846-868)
+        { Span sp(c->tr.t_in); memcpy(c->in.p + c->in_len, s, take); }              // pinned staging (replaces tmpIn, lz4frame.c:846-868)
         c->in_len += take; s += take; left -= take;
         if (c->in_len == c->batch && !c->prefs.autoFlush) {
-            size_t r = emit_staged(c, c->in_len, dst + written, cap - written);
+            size_t r = collect_flight(c, dst + written, cap - written);              // the batch before this one
             if (b2lz4_is_error(r)) return r;
-            written += r; c->in_len = 0;
+            written += r;
+            r = launch_staged(c, c->in_len);
+            if (b2lz4_is_error(r)) return r;
+            c->in_len = 0;
         }
     }
     if (c->prefs.autoFlush && c->in_len) {
@@ -200,12 +294,15 @@ size_t LZ4F_compressUpdate(LZ4F_cctx* c, void* dstBuffer, size_t cap, const void
 size_t LZ4F_flush(LZ4F_cctx* c, void* dstBuffer, size_t cap, const LZ4F_compressOptions_t* opt) {
     (void)opt;
     if (!c || !c->begun) return ec(E_GENERIC);
-    if (c->in_len == 0) return 0;                                                    // lz4frame.c:945
-    if (cap < blocks_bound(c->in_len, c->block_size, c->bp.block_checksum != 0)) return ec(E_dstMaxSize_tooSmall);
-    size_t r = emit_staged(c, c->in_len, (uint8_t*)dstBuffer, cap);
+    uint8_t* dst = (uint8_t*)dstBuffer;
+    size_t w = collect_flight(c, dst, cap);                                          // the batch still on the GPU comes first
+    if (b2lz4_is_error(w)) return w;
+    if (c->in_len == 0) return w;                                                    // lz4frame.c:945
+    if (cap - w < blocks_bound(c->in_len, c->block_size, c->bp.block_checksum != 0)) return ec(E_dstMaxSize_tooSmall);
+    size_t r = emit_staged(c, c->in_len, dst + w, cap - w);
     if (b2lz4_is_error(r)) return r;
     c->in_len = 0;
-    return r;
+    return w + r;
 }
 
 size_t LZ4F_compressEnd(LZ4F_cctx* c, void* dstBuffer, size_t cap, const LZ4F_compressOptions_t* opt) {
@@ -241,6 +338,9 @@ struct LZ4F_dctx_s {
     uint8_t hdr[HEADER_MAX]; uint32_t hdr_len = 0;          // header / small fixed-size elements being collected
     b2lz4_frame_info info{};
     Pinned in;  size_t in_len = 0;                           // whole blocks (+ the one being collected)
+    Pinned in2, out2;                                        // the batch in flight reads in2 and writes out2
+    std::future<size_t> job; bool flight = false;            // at most one batch is on the GPU while the caller drains `out`
+    bool check_sum = false; uint32_t stored_sum = 0;         // content checksum read from the stream, compared when all is decoded
     size_t complete_end = 0; uint32_t n_complete = 0;        // end of the last whole block in `in`, how many there are
     size_t need = 0;                                         // bytes still missing for the element being collected
     uint64_t skip_left = 0;
@@ -249,34 +349,60 @@ struct LZ4F_dctx_s {
     bool first = true;
     size_t pre_acked = 0;                                    // input bytes already buffered but reported as unconsumed
     size_t batch = 0;
+    Trace tr;
 };
 
 namespace {
 
 void dctx_reset(LZ4F_dctx_s* d) {
+    if (d->flight) { d->job.wait(); (void)d->job.get(); d->flight = false; }
     d->stage = DS_HEADER; d->hdr_len = 0; d->in_len = 0; d->complete_end = 0; d->n_complete = 0; d->need = 0;
     d->skip_left = 0; d->out_len = d->out_pos = 0; d->total_out = 0; d->first = true; d->pre_acked = 0;
+    d->check_sum = false; d->stored_sum = 0;
 }
 
-// decode the whole blocks collected so far
+bool job_done(LZ4F_dctx_s* d) { return d->job.wait_for(std::chrono::seconds(0)) == std::future_status::ready; }
+
+// the batch in flight has to finish: its output becomes the one handed out (only called when `out` is drained)
+size_t collect(LZ4F_dctx_s* d) {
+    if (!d->flight) return 0;
+    Span sp(d->tr.t_gpu);
+    const size_t r = d->job.get();
+    d->flight = false;
+    if (b2lz4_is_error(r)) return r;
+    std::swap(d->out, d->out2);
+    d->out_len = r; d->out_pos = 0; d->total_out += r;
+    return 0;
+}
+
+// Decode the whole blocks collected so far — on a helper thread, so that the GPU works on this batch while the caller
+// drains the previous one and feeds the next (the calls of this layer are host copies for the most part, B2LZ4_TRACE).
+// Only called when `out` is drained; the batch before this one, if still in flight, is collected first.
 size_t decode_batch(LZ4F_dctx_s* d) {
+    size_t r = collect(d);
+    if (b2lz4_is_error(r)) return r;
     if (d->n_complete == 0) return 0;
+    ++d->tr.batches;
     if (!d->gpu) {
         b2lz4_prefs bp; b2lz4_default_prefs(&bp); bp.use_index = 0;
-        size_t r = b2lz4_create(&d->gpu, device_index(), &bp);
+        r = b2lz4_create(&d->gpu, device_index(), &bp);
         if (b2lz4_is_error(r)) return r;
         r = apply_devices(d->gpu);
         if (b2lz4_is_error(r)) return r;
     }
     const size_t cap = (size_t)d->n_complete * d->info.block_size;
-    if (!d->out.ensure(cap + 16)) return ec(E_allocation_failed);
-    size_t r = b2lz4_decompress_blocks_host(d->gpu, &d->info, d->in.p, d->complete_end, d->out.p, cap,
-                                            d->first ? B2LZ4_STREAM_FIRST : 0u);
-    if (b2lz4_is_error(r)) return r;
-    d->first = false;
-    d->out_len = r; d->out_pos = 0; d->total_out += r;
-    memmove(d->in.p, d->in.p + d->complete_end, d->in_len - d->complete_end);
-    d->in_len -= d->complete_end; d->complete_end = 0; d->n_complete = 0;
+    if (!d->out2.ensure(cap + 16, 0, true)) return ec(E_allocation_failed);
+    // the bytes after the last whole block move to the other staging buffer, which becomes the one being filled
+    const size_t tail = d->in_len - d->complete_end;
+    if (!d->in2.ensure(std::max(tail + 8, d->in.cap / 2))) return ec(E_allocation_failed);
+    memcpy(d->in2.p, d->in.p + d->complete_end, tail);
+    std::swap(d->in, d->in2);
+    b2lz4_ctx* gpu = d->gpu; const b2lz4_frame_info info = d->info;
+    const uint8_t* src = d->in2.p; const size_t n = d->complete_end; uint8_t* dst = d->out2.p;
+    const unsigned flags = d->first ? B2LZ4_STREAM_FIRST : 0u;
+    d->job = std::async(std::launch::async, [=]() { return b2lz4_decompress_blocks_host(gpu, &info, src, n, dst, cap, flags); });
+    d->flight = true; d->first = false;
+    d->in_len = tail; d->complete_end = 0; d->n_complete = 0;
     return 0;
 }
 
@@ -306,8 +432,13 @@ LZ4F_errorCode_t LZ4F_createDecompressionContext(LZ4F_dctx** dctxPtr, unsigned v
 LZ4F_errorCode_t LZ4F_freeDecompressionContext(LZ4F_dctx* d) {
     if (!d) return 0;                                                                // lz4frame.c:1081
     const size_t stage = (size_t)d->stage;                                          // the reference returns the stage, not an error
+    if (d->flight) { d->job.wait(); (void)d->job.get(); d->flight = false; }
+    d->tr.report("dctx");
+    const double t0 = trace_on() ? Trace::now() : 0;
     b2lz4_destroy(d->gpu);
-    d->in.release(); d->out.release();
+    const double t1 = trace_on() ? Trace::now() : 0;
+    d->in.release(); d->out.release(); d->in2.release(); d->out2.release();
+    if (trace_on()) fprintf(stderr, "[b2lz4 dctx] free: engine context %.3f s, staging %.3f s\n", t1 - t0, Trace::now() - t1);
     delete d;
     return stage == DS_DONE ? 0 : stage;
 }
@@ -354,6 +485,8 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
     uint8_t* dst = (uint8_t*)dstBuffer;
     const size_t srcSize = src ? *srcSizePtr : 0, dstCap = dst ? *dstSizePtr : 0;
     size_t consumed = 0, produced = 0;
+    ++d->tr.calls;
+    Span whole(d->tr.t_all);
     *srcSizePtr = 0; *dstSizePtr = 0;
     auto fail = [&](size_t e) { dctx_reset(d); return e; };
     {   // bytes taken in an earlier call but handed back so that the caller comes again for the pending output
@@ -363,9 +496,15 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
     for (;;) {
         if (d->out_pos < d->out_len) {                                               // hand out decoded bytes first
             const size_t k = std::min(dstCap - produced, d->out_len - d->out_pos);
-            memcpy(dst + produced, d->out.p + d->out_pos, k);
+            { Span sp(d->tr.t_out); memcpy(dst + produced, d->out.p + d->out_pos, k); }
             produced += k; d->out_pos += k;
             if (d->out_pos < d->out_len) break;                                      // destination full
+        }
+        // `out` is drained: the batch in flight is taken over as soon as it is done, or when nothing else is left to do
+        if (d->flight && (d->stage == DS_DONE || job_done(d))) {
+            size_t r = collect(d);
+            if (b2lz4_is_error(r)) return fail(r);
+            continue;
         }
         if (d->stage == DS_DONE) break;
         if (consumed == srcSize) break;
@@ -408,10 +547,7 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
                 size_t r = decode_batch(d);
                 if (b2lz4_is_error(r)) return fail(r);
                 d->stage = DS_SUFFIX; d->need = d->info.content_checksum ? 4 : 0; d->hdr_len = 0;
-                if (d->need == 0) {
-                    if (d->info.has_content_size && d->info.content_size != d->total_out) return fail(ec(E_frameSize_wrong));
-                    d->stage = DS_DONE;
-                }
+                if (d->need == 0) d->stage = DS_DONE;                                // size / checksum are checked when all is decoded
                 break;
             }
             if (cs > d->info.block_size) return fail(ec(E_maxBlockSize_invalid));     // lz4frame.c:1489-1490
@@ -422,7 +558,8 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
         case DS_BLOCK_DATA: {
             if (!d->in.ensure(d->in_len + d->need + 8, d->in_len)) return fail(ec(E_allocation_failed));
             const size_t k = std::min(avail, d->need);
-            memcpy(d->in.p + d->in_len, src + consumed, k); d->in_len += k; consumed += k; d->need -= k;
+            { Span sp(d->tr.t_in); memcpy(d->in.p + d->in_len, src + consumed, k); }
+            d->in_len += k; consumed += k; d->need -= k;
             if (d->need) break;
             d->complete_end = d->in_len; ++d->n_complete;
             d->stage = DS_BLOCK_HEADER; d->need = 4;
@@ -437,18 +574,22 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
             const size_t k = std::min(avail, d->need);
             memcpy(d->hdr + d->hdr_len, src + consumed, k); d->hdr_len += (uint32_t)k; consumed += k; d->need -= k;
             if (d->need) break;
-            uint32_t h = 0;
-            if (d->first) h = 0x02CC5D05u;                                           // XXH32 of no bytes, seed 0 (frame without blocks)
-            else { size_t r = b2lz4_content_checksum(d->gpu, &h); if (b2lz4_is_error(r)) return fail(r); }
-            if (h != ld_le32(d->hdr)) return fail(ec(E_contentChecksum_invalid));
-            if (d->info.has_content_size && d->info.content_size != d->total_out) return fail(ec(E_frameSize_wrong));
+            d->stored_sum = ld_le32(d->hdr); d->check_sum = true;
             d->stage = DS_DONE;
             break;
         }
         default: break;
         }
     }
-    const bool pending = d->out_pos < d->out_len;
+    const bool pending = d->out_pos < d->out_len || (d->flight && d->stage == DS_DONE);
+    if (d->stage == DS_DONE && !pending) {                                           // everything is decoded: the frame's own checks
+        if (d->check_sum) {                                                          // content checksum (lz4frame.c:1734-1745)
+            uint32_t h = 0x02CC5D05u;                                                // XXH32 of no bytes, seed 0 (frame without blocks)
+            if (!d->first) { size_t r = b2lz4_content_checksum(d->gpu, &h); if (b2lz4_is_error(r)) return fail(r); }
+            if (h != d->stored_sum) return fail(ec(E_contentChecksum_invalid));
+        }
+        if (d->info.has_content_size && d->info.content_size != d->total_out) return fail(ec(E_frameSize_wrong));   // lz4frame.c:1715-1716
+    }
     if (pending && consumed == srcSize && consumed > 0) { --consumed; ++d->pre_acked; }   // make the caller come back for the rest
     *srcSizePtr = consumed; *dstSizePtr = produced;
     if (d->stage == DS_DONE && !pending) {                                           // frame complete (lz4frame.h:457-468: returns 0)
@@ -456,7 +597,10 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
         dctx_reset(d); d->pre_acked = keep;
         return 0;
     }
-    if (pending) return d->out_len - d->out_pos;                                     // hint: the caller may offer this much room
+    // hint: the caller may offer this much room.  Capped: the conduit sizes its next destination by the hint and then copies
+    // the bytes once more into the ByteString it yields (Conduit.hsc:665, 676) — a destination that stays in the CPU's cache
+    // makes that second copy cheap, a 64 MiB one does not
+    if (pending) return std::max<size_t>(1, std::min<size_t>(d->out_len - d->out_pos, HINT_MAX));
     return d->need ? d->need + (d->stage == DS_BLOCK_DATA ? 4 : 0) : 4;
 }
 
