@@ -491,7 +491,7 @@ static size_t pipe_chunk(const b2lz4_ctx* ctx, size_t n, size_t block_size) {
     return c;
 }
 // Chunk plan of a host-buffer call: start offsets in `unit`s, the last entry being the total.  Uniform chunks of `base`
-// units (a plan that starts and ends with quarter / half chunks was measured and bought nothing: 26.0 vs 26.0 ms per GiB).
+// units (a plan that starts and ends with quarter / half chunks was measured twice and bought 0 - 1 %: 23.2 vs 22.9 ms per GiB).
 static std::vector<size_t> plan_chunks(const b2lz4_ctx* ctx, size_t total, size_t base) {
     (void)ctx;
     std::vector<size_t> v{0};

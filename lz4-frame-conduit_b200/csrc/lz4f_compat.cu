@@ -230,7 +230,9 @@ static size_t launch_staged(LZ4F_cctx* c, size_t n) {
     ++c->tr.batches;
     b2lz4_ctx* gpu = c->gpu; const uint8_t* src = c->in2.p; uint8_t* dst = c->out.p;
     const unsigned flags = c->first ? B2LZ4_STREAM_FIRST : 0u;
-    c->job = std::async(std::launch::async, [=]() { return b2lz4_compress_blocks_host(gpu, src, n, dst, ocap, flags); });
+    auto run = [=]() { return b2lz4_compress_blocks_host(gpu, src, n, dst, ocap, flags); };
+    try { c->job = std::async(std::launch::async, run); }
+    catch (...) { std::promise<size_t> pr; pr.set_value(run()); c->job = pr.get_future(); }      // no thread to be had: run it here
     c->flight = true; c->first = false;
     return 0;
 }
@@ -400,7 +402,9 @@ size_t decode_batch(LZ4F_dctx_s* d) {
     b2lz4_ctx* gpu = d->gpu; const b2lz4_frame_info info = d->info;
     const uint8_t* src = d->in2.p; const size_t n = d->complete_end; uint8_t* dst = d->out2.p;
     const unsigned flags = d->first ? B2LZ4_STREAM_FIRST : 0u;
-    d->job = std::async(std::launch::async, [=]() { return b2lz4_decompress_blocks_host(gpu, &info, src, n, dst, cap, flags); });
+    auto run = [=]() { return b2lz4_decompress_blocks_host(gpu, &info, src, n, dst, cap, flags); };
+    try { d->job = std::async(std::launch::async, run); }
+    catch (...) { std::promise<size_t> pr; pr.set_value(run()); d->job = pr.get_future(); }      // no thread to be had: run it here
     d->flight = true; d->first = false;
     d->in_len = tail; d->complete_end = 0; d->n_complete = 0;
     return 0;
