@@ -332,7 +332,7 @@ constexpr uint32_t DEC_PAUSED = 0xFFFFFFFEu;   // decode_piece: stopped in front
 constexpr uint32_t HUGE_MATCH = 512u;          // overlapping matches at least this long are filled outside the sequence loop
 constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
 #ifndef B2_DEC_LANE_CAP
-#define B2_DEC_LANE_CAP 32
+#define B2_DEC_LANE_CAP 24
 #endif
 constexpr uint32_t LANE_CAP = B2_DEC_LANE_CAP;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
 

@@ -48,7 +48,7 @@ constexpr uint32_t ENC_PRIME_STRIDE = B2_ENC_PRIME_STRIDE;   // priming inserts 
 #endif
 constexpr uint32_t ENC_MINLEN = B2_ENC_MINLEN;               // matches shorter than this (forward + backward bytes seen at verify time) are ignored
 #ifndef B2_ENC_LAZY
-#define B2_ENC_LAZY 24
+#define B2_ENC_LAZY 32
 #endif
 constexpr uint32_t ENC_LAZY = B2_ENC_LAZY;                   // matches shorter than this give way to a longer one 1..3 positions later (0 = off)
 constexpr uint32_t ENC_PRIME_NEAR = 4096u;                   // history primed before the unit is known to be compressible
