@@ -454,6 +454,13 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
             cap_tables = std::max(fi.need_blocks, fi.need_pieces) + 16;
             ++ctx->stats.retries; continue;
         }
+        if (fi.indexed && (mode & SCAN_USE_INDEX) && dr.err != OK && attempt < 3) {
+            // the index is side information in a skippable frame behind the frame: whatever is wrong with it (entries that
+            // pass the structural checks but point at the wrong bytes) must not make a valid frame fail — decode without it;
+            // if the frame itself is bad, that run reports the real error
+            mode &= ~SCAN_USE_INDEX;
+            ++ctx->stats.retries; continue;
+        }
         if (fi.err == OK && !fi.layout_known && fi.n_chains > 1 && !(mode & SCAN_SINGLE_CHAIN) &&
             (dr.err != OK || !dr.layout_ok) && attempt < 3) {
             // the "block b starts at b * blockSize" layout did not hold (a middle block decoded short: flushed
@@ -774,6 +781,10 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* d
     if (!ok || !f.desc.block_independent || f.blocks.size() <= per_group)
         return decompress_host_whole(ctx, src_, n, dst, cap, consumed);           // linked frames, small frames, anything odd
     r = decompress_host_groups(ctx, src, f, per_group, dst, cap, HOSTC_FRAME);
+    if (b2lz4_is_error(r) && f.ix_blocks) {                                          // a bad index must not fail a valid frame: once more without it
+        HostFrame g;
+        if (host_scan(src, n, false, g)) { g.consumed = f.consumed; r = decompress_host_groups(ctx, src, g, per_group, dst, cap, HOSTC_FRAME); }
+    }
     if (!b2lz4_is_error(r) && consumed) *consumed = f.consumed;
     return r;
 }

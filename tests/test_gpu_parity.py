@@ -125,6 +125,77 @@ def test_decode_rejects_corruption(codec, oracle, manifest, pkg):
                 assert got == want, (kind, trial)
 
 
+def test_decode_fuzz_never_writes_outside_the_destination(codec, oracle, manifest, pkg, gen):
+    """Bounds check of our own (compute-sanitizer is not available on the GPU pool): corrupted and truncated frames are
+    decoded DEVICE-resident into a destination of exactly the payload's size that sits between two guard zones, and
+    the compressed input has a guard behind it as well.  Whatever the verdict, the guards must be untouched, and
+    verdict and bytes must agree with the oracle (lz4/tests/frametest.c:1044-1073, fuzzer.c:1040-1053)."""
+    import torch
+    rnd = random.Random(2026)
+    G = 1 << 16
+    cases = [(payload(manifest, "mixed166k"), golden_bytes(manifest["mixed166k"]["frames"][k]["file"])) for k in ("cli_B4_BX", "conduit", "cli")]
+    d2 = gen_bytes(gen, "loglike", 700000)
+    for prefs in (dict(block_size_id=4, write_index=1), dict(block_size_id=5, sub_block_log2=16, write_index=0, block_checksum=1)):
+        codec.set_prefs(**{**dict(block_size_id=7, block_checksum=0, content_checksum=0, content_size=0, sub_block_log2=18,
+                                  write_index=1, use_index=1), **prefs})
+        cases.append((d2, codec.compress_bytes(d2)))
+    codec.set_prefs(block_size_id=7, block_checksum=0, content_checksum=0, content_size=0, sub_block_log2=18, write_index=1, use_index=1)
+    for d, good in cases:
+        n = len(d)
+        for trial in range(30):
+            b = bytearray(good)
+            kind = trial % 5
+            if kind == 4:
+                b = b[:rnd.randrange(7, len(b))]
+            elif kind == 3:                                  # length fields: tokens / extension bytes forced to 255
+                for _ in range(rnd.randint(1, 4)):
+                    b[rnd.randrange(7, len(b))] = 0xFF
+            else:
+                for _ in range(rnd.randint(1, 3)):
+                    b[rnd.randrange(7, len(b))] ^= 1 << rnd.randrange(8)
+            b = bytes(b)
+            want, _ = orc_decode(oracle, b, n)
+            src = torch.full((len(b) + G,), 0xA5, dtype=torch.uint8, device="cuda")
+            src[:len(b)] = torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
+            dst = torch.full((n + 2 * G,), 0xEE, dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+            try:
+                r, _ = codec.decompress_device(src.data_ptr(), len(b), dst.data_ptr() + G, n)
+                got = bytes(dst[G:G + r].cpu().numpy())
+            except pkg.Lz4FrameError:
+                got = None
+            torch.cuda.synchronize()
+            assert int(dst[:G].min()) == 0xEE and int(dst[G + n:].min()) == 0xEE, ("guard overwritten", trial)
+            assert int(dst[:G].max()) == 0xEE and int(dst[G + n:].max()) == 0xEE, ("guard overwritten", trial)
+            assert int(src[len(b):].min()) == 0xA5 and int(src[len(b):].max()) == 0xA5
+            if isinstance(want, int):
+                assert got is None, (trial, want)
+            else:
+                assert got == want, trial
+
+
+def test_corrupt_index_never_fails_a_valid_frame(codec, gen):
+    """The B2IX index travels in a skippable frame BEHIND the frame (lz4_Frame_format.md:298-335): a stock decoder ignores
+    it, so whatever is wrong with it must not change the verdict on the frame.  An entry that passes the structural
+    checks but points one byte off makes the indexed decode fail; the engine then decodes without the index — in the
+    single-call device path and in the chunked host-buffer path (frame > one pipeline chunk)."""
+    d = gen_bytes(gen, "loglike", 96 << 20)
+    codec.set_prefs(block_size_id=7, block_checksum=0, content_checksum=0, content_size=0, sub_block_log2=17, write_index=1, use_index=1)
+    fr = bytearray(codec.compress_bytes(d))
+    at = len(fr) - 8 - 8                                         # token offset of the last chain of the last block
+    tok = int.from_bytes(fr[at:at + 4], "little")
+    assert tok > 0
+    fr[at:at + 4] = (tok + 1).to_bytes(4, "little")
+    out, consumed = codec.decompress_bytes(bytes(fr), max_out=len(d))          # host buffers: chunked pipeline, index slices
+    assert out == d
+    small = gen_bytes(gen, "loglike", 9 << 20)
+    fr = bytearray(codec.compress_bytes(small))
+    at = len(fr) - 8 - 8
+    fr[at:at + 4] = (int.from_bytes(fr[at:at + 4], "little") + 1).to_bytes(4, "little")
+    out, _ = codec.decompress_bytes(bytes(fr), max_out=len(small))             # one call on the device
+    assert out == small and codec.stats().retries >= 1
+
+
 def test_decode_malformed_blocks(codec, pkg):
     # lz4/tests/fuzzer.c:1040-1053: the 17-byte block that must be rejected, wrapped in a frame
     hdr = bytes.fromhex("04224d18604082")
