@@ -415,7 +415,10 @@ size_t header_done(LZ4F_dctx_s* d) {
     size_t r = b2lz4_frame_header_parse(d->hdr, d->hdr_len, &d->info);
     if (b2lz4_is_error(r)) return r;
     d->stage = DS_BLOCK_HEADER; d->hdr_len = 0; d->need = 4;
-    d->batch = batch_bytes();
+    // a foreign block is decoded by ONE warp (no side information to start inside it), at ~0.1 GB/s: what makes a batch
+    // fast is the number of blocks in it, so batches of large blocks are sized by count (64 blocks, at most 256 MiB)
+    d->batch = std::max(batch_bytes(), std::min<size_t>((size_t)64 * d->info.block_size, (size_t)256 << 20));
+    if (getenv("B2LZ4_BATCH_MB")) d->batch = batch_bytes();
     return 0;
 }
 

@@ -36,3 +36,20 @@ if ref is not None:
     d, td = t(lambda: ours.ref_conduit_decompress(comp, c, back, n + 64, 65536, C.byref(used)))
     assert d == m and back.raw[m - 4096:m] == src.raw[m - 4096:m]
     print(f"b200 LZ4F_decompress on the reference-made frame (linked 64 KB blocks, {m >> 20} MiB): {m / td / 1e9:.3f} GB/s", flush=True)
+
+cli = os.path.join(ROOT, "oracle", "_ref", "lz4")
+if os.path.exists(cli):
+    import subprocess, tempfile
+    os.environ.pop("B2LZ4_BATCH_MB", None)                   # library default: batches of large blocks are sized by block count
+    m = min(n, 512 << 20)
+    with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as td:
+        raw = os.path.join(td, "raw"); open(raw, "wb").write(src.raw[:m])
+        for flags, what in ((["-B7", "--no-frame-crc"], "stock CLI frame, 4 MB independent blocks, no content checksum"),
+                            ([], "stock CLI default frame (4 MB blocks + content checksum)")):
+            fr = subprocess.run([cli, "-c", *flags, raw], capture_output=True, check=True).stdout
+            used = C.c_size_t(0)
+            for lib, name in ((ours, "b200 LZ4F_decompress"), (ref, "reference library")):
+                if lib is None: continue
+                d, td_ = t(lambda: lib.ref_conduit_decompress(fr, len(fr), back, n + 64, 65536, C.byref(used)))
+                assert d == m and back.raw[m - 4096:m] == src.raw[m - 4096:m], (name, d)
+                print(f"{name} on a {what} ({m >> 20} MiB): {m / td_ / 1e9:.2f} GB/s", flush=True)
