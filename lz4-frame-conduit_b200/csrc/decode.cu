@@ -331,6 +331,9 @@ __device__ __forceinline__ void warp_match_overlap(uint8_t* d, uint32_t offset, 
 constexpr uint32_t DEC_PAUSED = 0xFFFFFFFEu;   // decode_piece: stopped in front of a huge overlapping match (see Cursor::p_*)
 constexpr uint32_t HUGE_MATCH = 512u;          // overlapping matches at least this long are filled outside the sequence loop
 constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
+#ifndef B2_DEC_PREFETCH
+#define B2_DEC_PREFETCH 2      // 128-byte lines of the compressed stream requested ahead at every window refill
+#endif
 #ifndef B2_DEC_LANE_CAP
 #define B2_DEC_LANE_CAP 24
 #endif
@@ -384,6 +387,11 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
                     wb = (int32_t)tip - (int32_t)((uintptr_t)(sp + tip) & 3u);
                     const uint8_t* g = sp + wb;
                     __syncwarp();
+#if B2_DEC_PREFETCH
+                    // the lines the NEXT refills (and this batch's literal copies) will want: a warp reads its stream strictly
+                    // forward, one dependent DRAM round trip per window if nobody asks ahead
+                    if (lane < (uint32_t)B2_DEC_PREFETCH && g + 256u + 128u * lane < c.src_end) prefetch_l1(g + 256u + 128u * lane);
+#endif
                     const uint32_t w0 = (g + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 4u * lane) : 0u;
                     const uint32_t w1 = (g + 128u + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 128u + 4u * lane) : 0u;
                     ((uint32_t*)win)[lane] = w0; ((uint32_t*)win)[32u + lane] = w1;
