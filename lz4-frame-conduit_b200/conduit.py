@@ -97,17 +97,18 @@ def compress_yield_immediately(chunks, prefs=None):
         hdr = C.create_string_buffer(LZ4F_HEADER_SIZE_MAX)
         n = _handle(lib, lib.LZ4F_compressBegin(ctx.p, hdr, LZ4F_HEADER_SIZE_MAX, C.byref(prefs)))
         yield hdr.raw[:n]
+        # the reference allocates LZ4F_compressBound(len) bytes per piece (allocaBytes, :385, :400); this library's bound covers
+        # two whole batches, so ONE buffer of the largest bound is kept for the stream instead of a fresh one per 16 KB
+        cap = _handle(lib, lib.LZ4F_compressBound(_BS_CHUNK, C.byref(prefs)))
+        out = (C.c_char * cap)()
+        base = C.addressof(out)
         for bs in chunks:
             for piece in bs_chunks_of(_BS_CHUNK, bytes(bs)):
-                cap = _handle(lib, lib.LZ4F_compressBound(len(piece), C.byref(prefs)))
-                out = C.create_string_buffer(cap)
-                w = _handle(lib, lib.LZ4F_compressUpdate(ctx.p, out, cap, piece, len(piece), None))
+                w = _handle(lib, lib.LZ4F_compressUpdate(ctx.p, base, cap, piece, len(piece), None))
                 if w:
-                    yield out.raw[:w]
-        cap = _handle(lib, lib.LZ4F_compressBound(0, C.byref(prefs)))
-        out = C.create_string_buffer(cap)
-        w = _handle(lib, lib.LZ4F_compressEnd(ctx.p, out, cap, None))
-        yield out.raw[:w]
+                    yield C.string_at(base, w)
+        w = _handle(lib, lib.LZ4F_compressEnd(ctx.p, base, cap, None))
+        yield C.string_at(base, w)
 
 
 def compress_with_out_buffer_size(buffer_size, chunks, prefs=None):
