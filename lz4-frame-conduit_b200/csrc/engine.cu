@@ -484,7 +484,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
 
 // -------------------------------------------------------------------------------------- host buffers
 // pipeline shape of the host-buffer calls: B2LZ4_LANES chunks in flight (default 4), B2LZ4_PIPE_MB per chunk (default: an
-// eighth of the stream, 32..256 MiB)
+// sixteenth of the stream, 32..256 MiB)
 static int pipe_lanes(const b2lz4_ctx* ctx) {
     const char* e = getenv("B2LZ4_LANES"); int v = e ? atoi(e) : 4;
     if (ctx->n_devs > 1 && !e) v = std::max(v, 2 * ctx->n_devs);      // at least two chunks in flight per GPU
