@@ -483,7 +483,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
 }
 
 // -------------------------------------------------------------------------------------- host buffers
-// pipeline shape of the host-buffer calls: B2LZ4_LANES chunks in flight (default 4), B2LZ4_PIPE_MB per chunk (default: an
+// pipeline shape of the host-buffer calls: B2LZ4_LANES chunks in flight (default 4), B2LZ4_PIPE_MB per chunk (default: a
 // sixteenth of the stream, 32..256 MiB)
 static int pipe_lanes(const b2lz4_ctx* ctx) {
     const char* e = getenv("B2LZ4_LANES"); int v = e ? atoi(e) : 4;
