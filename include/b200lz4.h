@@ -29,11 +29,11 @@ typedef struct b2lz4_ctx b2lz4_ctx;
  * (src/Codec/Compression/LZ4/CTypes.hsc:155-232; lz4/lib/lz4frame.h:169-192) that make sense for
  * an independent-block GPU encoder, plus two knobs of this implementation. */
 typedef struct {
-    uint32_t block_size_id;     /* 0 = default (4 MB); 4..7 = 64 KB, 256 KB, 1 MB, 4 MB (lz4frame.h:115-124) */
+    uint32_t block_size_id;     /* 4..7 = 64 KB, 256 KB, 1 MB, 4 MB (lz4frame.h:115-124); 0 = 4 MB; b2lz4_default_prefs sets 5 */
     uint32_t block_checksum;    /* XXH32 after every block (lz4frame.h:186-192 blockChecksumFlag) */
     uint32_t content_checksum;  /* XXH32 of the whole content after the EndMark */
     uint32_t content_size;      /* 1 = store the content size in the frame header (one-shot calls only) */
-    uint32_t sub_block_log2;    /* independent sub-block size inside a block: 0 = default (17 = 128 KB), 16..22 */
+    uint32_t sub_block_log2;    /* independent sub-block size inside a block: 16..22; 0 = 17 (128 KB); b2lz4_default_prefs sets 18 */
     uint32_t write_index;       /* 1 = append the B2IX skippable index frame ("seekable" frame: block table + sub-block
                                    entry points, lets the decoder run every sub-block in parallel).  Default 0: the
                                    stock lz4 CLI skips skippable frames in files but fails on pipes (lz4io.c:1124-1133). */

@@ -312,10 +312,10 @@ def test_encode_ratio_vs_reference_default(codec, ref, gen, datagen):
 def test_default_prefs_emit_plain_frames(pkg, lz4_cli, gen):
     """Drop-in default: no trailing index frame, `lz4 -d` on a pipe accepts the output (test/Main.hs:60-85)."""
     with pkg.Codec(0) as c:
-        assert c.prefs.write_index == 0 and c.prefs.block_size_id == 7
+        assert c.prefs.write_index == 0 and c.prefs.block_size_id == 5
         d = gen_bytes(gen, "loglike", 3 << 20)
         fr = c.compress_bytes(d)
-        assert fr[:7].hex() == "04224d18607073" and fr[-4:] == bytes(4)
+        assert fr[:7].hex() == "04224d186050fb" and fr[-4:] == bytes(4)
         if lz4_cli:
             r = subprocess.run([lz4_cli, "-d"], input=fr, capture_output=True)
             assert r.returncode == 0 and r.stdout == d

@@ -10,7 +10,7 @@ gib = float(sys.argv[1]) if len(sys.argv) > 1 else 5.0
 ngpu = int(sys.argv[2]) if len(sys.argv) > 2 else torch.cuda.device_count()
 n = int(gib * (1 << 30))
 gen = C.CDLL(os.path.join(ROOT, "tools", "libb2gen.so")); gen.b2gen_loglike.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
-c = pkg.Codec(0, content_checksum=int(os.environ.get("SUM", "0")))
+c = pkg.Codec(0, content_checksum=int(os.environ.get("SUM", "0")))     # library defaults: plain frame, 256 KB blocks
 c.set_devices(list(range(ngpu)))
 h_in = torch.empty(n, dtype=torch.uint8).pin_memory()
 for i in range(0, n, 1 << 30):                                   # per-GiB reseeding
@@ -28,7 +28,8 @@ ok = (r == n and used == cs)
 step = 1 << 28
 for i in range(0, n, step):
     ok = ok and torch.equal(h_in[i:i + step], h_b[i:i + step])
-print(json.dumps({"workload": f"config3 shape: one frame of {gib} GiB log-like (per-GiB reseeded), 4 MB independent blocks, host in -> host out",
+bs = (1 << (8 + 2 * c.prefs.block_size_id)) >> 10
+print(json.dumps({"workload": f"config3 shape: one frame of {gib} GiB log-like (per-GiB reseeded), {bs} KB independent blocks, host in -> host out",
                   "n_gpus": ngpu, "bytes": n, "frame_bytes": cs, "ratio": n / cs, "bit_exact": bool(ok),
                   "compress_host_GBps": n * K / (t1 - t0) / 1e9, "decompress_host_GBps": n * K / (t2 - t1) / 1e9,
                   "roundtrip_GBps": n * K / (t2 - t0) / 1e9, "content_checksum": int(os.environ.get("SUM", "0"))}))

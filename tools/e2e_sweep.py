@@ -6,7 +6,7 @@ import torch
 pkg = importlib.import_module("lz4-frame-conduit_b200")
 n = (int(sys.argv[1]) if len(sys.argv) > 1 else 1024) << 20
 gen = C.CDLL(os.path.join(ROOT, "tools", "libb2gen.so")); gen.b2gen_loglike.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
-c = pkg.Codec(0, write_index=int(os.environ.get("IDX", "1")))
+c = pkg.Codec(0, block_size_id=7, sub_block_log2=17, write_index=int(os.environ.get("IDX", "1")))   # the bench shape
 h_in = torch.empty(n, dtype=torch.uint8).pin_memory(); gen.b2gen_loglike(h_in.data_ptr(), n, 0x10C5)
 cap = pkg.compress_bound(n, c.prefs)
 h_c = torch.empty(cap, dtype=torch.uint8).pin_memory(); h_b = torch.empty(n, dtype=torch.uint8).pin_memory()
