@@ -7,7 +7,9 @@ import random
 
 import pytest
 
-from conftest import OrcDesc, golden_bytes, orc_decode, ref_conduit_decode, gen_bytes
+import os
+
+from conftest import ROOT, OrcDesc, golden_bytes, orc_decode, ref_conduit_decode, gen_bytes
 
 
 def payload(man, name):
@@ -183,3 +185,24 @@ def test_xxh32_streaming_vs_reference(oracle, ref, gen):
     d = gen_bytes(gen, "random", 100003)
     for n in (0, 1, 15, 16, 17, 31, 32, 33, 1000, 100003):
         assert oracle.orc_xxh32(d, n, 0) == ref.ref_xxh32(d, n, 0) == ref.ref_xxh32_stream(d, n, 0, 7)
+
+
+def test_prepass_model_on_golden_frames(manifest, tmp_path):
+    """tools/prepass_model.c (CPU model of the token-link pre-pass planned for foreign blocks): on frames the
+    stock CLI made, chaining the per-window exit tables from entry 0 must land on true sequence boundaries only and reproduce
+    the block's end and output size — for several window sizes."""
+    import subprocess
+    exe = tmp_path / "prepass_model"
+    subprocess.run(["gcc", "-O2", "-o", str(exe), os.path.join(ROOT, "tools", "prepass_model.c")], check=True)
+    n = 0
+    for name in ("mixed166k", "datagen200k"):
+        for kind in ("cli", "cli_B4_BX"):
+            fr = manifest[name]["frames"].get(kind)
+            if not fr:
+                continue
+            path = os.path.join(ROOT, "tests", "golden", fr["file"])
+            for w in (64, 128, 1024):
+                r = subprocess.run([str(exe), path, str(w)], capture_output=True, text=True)
+                assert r.returncode == 0 and "true sequence boundary: OK" in r.stdout, (name, kind, w, r.stderr)
+                n += 1
+    assert n >= 6
