@@ -401,7 +401,7 @@ def main():
     if not args.skip_cpu:
         lib = ref_lib()
         if lib is not None:
-            sample = min(n, 256 << 20)
+            sample = min(n, 1 << 30)                     # the whole stream of config 2: ~2.5 s of one core
             tc, td, cs = ref_roundtrip(lib, host_in.data_ptr(), sample, 1)
             cpu = {"value": sample / (tc + td) / 1e9, "unit": UNIT, "cores": 1, "kind": "reference",
                    "sample": f"first {sample >> 20} MiB of the same stream, reference conduit replay (Conduit.hsc call sequence on the unmodified lz4 library), 1 thread",
