@@ -206,3 +206,29 @@ def test_prepass_model_on_golden_frames(manifest, tmp_path):
                 assert r.returncode == 0 and "true sequence boundary: OK" in r.stdout, (name, kind, w, r.stderr)
                 n += 1
     assert n >= 6
+
+
+def test_dep_model_on_golden_frames(manifest, tmp_path):
+    """tools/dep_model.c (CPU model of the match dependencies inside foreign blocks): it walks every
+    stock-CLI golden frame without finding a malformed block; with a piece as large as the block nothing can reach in front
+    of a piece, with small pieces something does; and the per-lane dataflow variant of its timing model is never slower
+    than the watermark variant."""
+    import re
+    import subprocess
+    exe = tmp_path / "dep_model"
+    subprocess.run(["gcc", "-O2", "-o", str(exe), os.path.join(ROOT, "tools", "dep_model.c")], check=True)
+    n = 0
+    for name in ("mixed166k", "datagen200k"):
+        fr = manifest[name]["frames"].get("cli")
+        if not fr:
+            continue
+        path = os.path.join(ROOT, "tests", "golden", fr["file"])
+        whole = subprocess.run([str(exe), path, str(4 << 20)], capture_output=True, text=True)
+        small = subprocess.run([str(exe), path, "4096"], capture_output=True, text=True)
+        assert whole.returncode == 0 and small.returncode == 0, (whole.stderr, small.stderr)
+        direct = lambda out: int(re.search(r"in front of their piece: (\d+)", out).group(1))
+        assert direct(whole.stdout) == 0 and direct(small.stdout) > 0
+        x = [float(v) for v in re.findall(r"K=32: ([0-9.]+) x", small.stdout)]
+        assert len(x) == 3 and x[2] >= x[0] >= 1.0, small.stdout
+        n += 1
+    assert n >= 1
