@@ -237,20 +237,21 @@ def test_dep_model_on_golden_frames(manifest, tmp_path):
 def test_lane_decode_model_on_golden_frames(manifest, tmp_path):
     """tools/lane_decode_model.c (functional CPU model of the decode scheme planned for foreign blocks, DESIGN.md §9 item 1:
     batches of 32 sequences in ticket order, one match per lane, each copied once ITS source bytes are final, state kept for
-    a ring of recent batches only): its output equals the serial decode on stock-CLI golden frames for several warp counts
-    and ring sizes, without deadlock."""
+    a ring of recent batches only): its output equals the serial decode on stock-CLI and reference-conduit golden frames
+    (independent blocks per block, linked-block frames as one unit) for several warp counts and ring sizes, without deadlock."""
     import subprocess
     exe = tmp_path / "lane_decode_model"
     subprocess.run(["gcc", "-O2", "-o", str(exe), os.path.join(ROOT, "tools", "lane_decode_model.c")], check=True)
     n = 0
-    for name in ("mixed166k", "datagen200k"):
-        for kind in ("cli", "cli_B4_BX"):
+    for name in ("mixed166k", "datagen200k", "random70k", "hellos", "thirteen", "b65537"):
+        for kind in ("cli", "cli_B4_BX", "cli_B4_BD", "conduit"):       # the last two are linked-block frames: one unit per frame
             fr = manifest[name]["frames"].get(kind)
             if not fr:
                 continue
             path = os.path.join(ROOT, "tests", "golden", fr["file"])
             for k, ring in ((1, 1), (3, 2), (8, 16), (32, 128)):
                 r = subprocess.run([str(exe), path, str(k), str(ring)], capture_output=True, text=True)
-                assert r.returncode == 0 and "equals the serial decode: OK" in r.stdout, (name, kind, k, ring, r.stdout, r.stderr)
+                ok = "equals the serial decode: OK" in r.stdout or "no compressed blocks" in r.stdout   # all-stored independent frames
+                assert r.returncode == 0 and ok, (name, kind, k, ring, r.stdout, r.stderr)
                 n += 1
-    assert n >= 8
+    assert n >= 40
