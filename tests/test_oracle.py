@@ -255,3 +255,38 @@ def test_lane_decode_model_on_golden_frames(manifest, tmp_path):
                 assert r.returncode == 0 and ok, (name, kind, k, ring, r.stdout, r.stderr)
                 n += 1
     assert n >= 40
+
+
+def test_tickets_model_on_golden_frames(manifest, tmp_path):
+    """tools/tickets_model.c (CPU model of the pre-pass kernels K1a-c): per-group tables with bounded
+    length runs (SLOW tokens), the stitch and the ticket emission give exactly the boundaries of sequences 0, 32, 64, ... of a
+    serial parse — on the golden frames and, where the stock CLI is built (oracle/_ref/lz4), on a frame with multi-megabyte
+    runs whose length codes are far longer than the bound."""
+    import re
+    import subprocess
+    exe = tmp_path / "tickets_model"
+    subprocess.run(["gcc", "-O2", "-o", str(exe), os.path.join(ROOT, "tools", "tickets_model.c")], check=True)
+    n = 0
+    for name in ("mixed166k", "datagen200k", "hellos", "b65537"):
+        for kind in ("cli", "cli_B4_BX", "cli_B4_BD", "conduit"):       # ticket positions do not depend on block linkage
+            fr = manifest[name]["frames"].get(kind)
+            if not fr:
+                continue
+            path = os.path.join(ROOT, "tests", "golden", fr["file"])
+            for g, run in ((1024, 64), (128, 8), (8, 1)):
+                r = subprocess.run([str(exe), path, str(g), str(run)], capture_output=True, text=True)
+                ok = "every 32nd sequence boundary: OK" in r.stdout or "no compressed blocks" in r.stdout
+                assert r.returncode == 0 and ok, (name, kind, g, run, r.stdout, r.stderr)
+                n += 1
+    assert n >= 30
+    cli = os.path.join(ROOT, "oracle", "_ref", "lz4")
+    if os.path.exists(cli):
+        import numpy as np
+        rng = np.random.default_rng(5)
+        text = bytes(rng.integers(97, 101, 300000, dtype=np.uint8))
+        raw = tmp_path / "runs.bin"
+        raw.write_bytes(text[:200000] + bytes(5000000) + bytes(rng.integers(0, 256, 100000, dtype=np.uint8)) + text[200000:] + b"\x07" * 70000)
+        subprocess.run([cli, "-f", "-q", str(raw), str(tmp_path / "runs.lz4")], check=True)
+        r = subprocess.run([str(exe), str(tmp_path / "runs.lz4"), "1024", "64"], capture_output=True, text=True)
+        assert r.returncode == 0 and "every 32nd sequence boundary: OK" in r.stdout, (r.stdout, r.stderr)
+        assert int(re.search(r"SLOW tokens on the chain (\d+)", r.stdout).group(1)) >= 2, r.stdout
