@@ -37,7 +37,7 @@ static uint32_t seq_of(const Seq* q, uint32_t nseq, uint32_t s) {
     return lo;
 }
 
-typedef struct { uint64_t units, ubytes, rounds, batches, batch_rounds, stall_ring, long_matches; uint32_t batch_rounds_max; } Stats;
+typedef struct { uint64_t units, ubytes, rounds, batches, batch_rounds, stall_ring, long_matches, checks, touched, matches; uint32_t batch_rounds_max; } Stats;
 
 /* decode one unit (an independent block, or a whole linked frame) the modelled way into `out` and compare with `ref` */
 static int run_model(const uint8_t* d, const Seq* q, uint32_t nseq, uint32_t usize, const uint8_t* ref, uint8_t* out, uint32_t K, uint32_t RING, Stats* st) {
@@ -64,9 +64,9 @@ static int run_model(const uint8_t* d, const Seq* q, uint32_t nseq, uint32_t usi
             for (uint32_t j = s0; j < s1; ++j) {
                 if (q[j].ml == 0 || (done[b] >> (j - s0) & 1u)) continue;
                 const uint32_t mo = q[j].o + q[j].ll, src = mo - q[j].off, span = q[j].ml < q[j].off ? q[j].ml : q[j].off;
-                int ok = 1;
+                int ok = 1; ++st->checks;
                 for (uint32_t x = seq_of(q, nseq, src); ok && x <= j && q[x].o < src + span; ++x) {      /* every sequence the range touches */
-                    const uint32_t xb = x / BATCH;
+                    const uint32_t xb = x / BATCH; ++st->touched;
                     if (xb + RING <= b) continue;                                   /* in front of the ring: final by construction */
                     if (!parsed[xb]) { ok = 0; break; }                             /* literals (and offsets) not there yet */
                     const uint32_t xm = q[x].o + q[x].ll;                           /* where x's match part starts */
@@ -90,7 +90,7 @@ static int run_model(const uint8_t* d, const Seq* q, uint32_t nseq, uint32_t usi
                 for (uint32_t j = s0; j < s1; ++j) if (rdy[k] >> (j - s0) & 1u) {
                     const uint32_t mo = q[j].o + q[j].ll;
                     for (uint32_t i = 0; i < q[j].ml; ++i) out[mo + i] = out[mo - q[j].off + i];
-                    done[b] |= 1u << (j - s0);
+                    done[b] |= 1u << (j - s0); ++st->matches;
                 }
             }
             const uint32_t full = (s1 - s0 == 32) ? 0xFFFFFFFFu : ((1u << (s1 - s0)) - 1u);
@@ -189,5 +189,7 @@ int main(int argc, char** argv) {
            "matches longer than 4 KB (want a warp-wide copy) %llu\n", K, RING, (double)st.batches / st.units, (double)st.rounds / st.units,
            (double)st.batches / st.rounds, (double)st.batch_rounds / st.batches, st.batch_rounds_max, (unsigned long long)st.stall_ring,
            (unsigned long long)st.long_matches);
+    printf("readiness checks per match %.2f (1 = ready at first look), sequences examined per check %.2f\n",
+           st.matches ? (double)st.checks / st.matches : 0.0, st.checks ? (double)st.touched / st.checks : 0.0);
     return 0;
 }
