@@ -81,6 +81,10 @@ int    b2lz4_device_count(void);
 /* ---- sizes (replaces LZ4F_compressBound / LZ4F_compressFrameBound, lz4frame.c:324-349, 370-381) */
 size_t b2lz4_compress_bound(size_t n, const b2lz4_prefs* prefs);
 
+/* upper bound of the decoded size of the first frame in src[0, n): number of blocks (host walk over the block header
+ * words, lz4frame.c:1470-1500) x block size.  What a caller without a content-size field sizes its destination by. */
+size_t b2lz4_decompress_bound(const void* src, size_t n);
+
 /* ---- host-only frame helpers: no GPU involved (replace lz4frame.c:663-701 and :1109-1198) */
 size_t b2lz4_frame_header_write(void* dst, size_t cap, const b2lz4_prefs* prefs, uint64_t content_size);
 size_t b2lz4_frame_header_parse(const void* src, size_t n, b2lz4_frame_info* info);   /* returns header size */

@@ -28,6 +28,14 @@
  * blocks, LZ4F_default block size means 256 KB, and the encoder works in batches (B2LZ4_BATCH_MB, default
  * 32 MiB, one on the GPU while the next is staged), so LZ4F_compressBound() is larger than the reference's
  * and output arrives in larger pieces, one batch late.
+ * LZ4F_decompress, details a caller may notice (none is used by Conduit.hsc, which only tests the result for 0, error, or
+ * "anything else"):
+ *   - while decoded bytes are waiting to be handed out, the return value is a hint for the NEXT DESTINATION size (at most
+ *     512 KB), not the next source size as in the reference (lz4frame.h:457-468 allows any non-zero "hint");
+ *   - when a call has taken all its input but still holds output, *srcSizePtr reports one byte fewer than was taken, so
+ *     that a caller that loops "until the input is consumed" comes back for the output; the library remembers the byte,
+ *     the caller must present it again (any correct caller does: it re-sends what was reported unconsumed);
+ *   - a skippable frame ends like any frame: the context is reset and the call returns 0 (lz4frame.c:1789-1799).
  * There is no CPU codec behind these symbols: without a usable CUDA device they return ERROR_cudaFailure.
  */
 #ifndef B200_LZ4FRAME_H

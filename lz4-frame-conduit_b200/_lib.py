@@ -45,6 +45,7 @@ SYMBOLS = {
     "b2lz4_default_prefs": (None, [C.POINTER(Prefs)]),
     "b2lz4_device_count": (C.c_int, []),
     "b2lz4_compress_bound": (_sz, [_sz, C.POINTER(Prefs)]),
+    "b2lz4_decompress_bound": (_sz, [_vp, _sz]),
     "b2lz4_frame_header_write": (_sz, [_vp, _sz, C.POINTER(Prefs), C.c_uint64]),
     "b2lz4_frame_header_parse": (_sz, [_vp, _sz, C.POINTER(FrameInfo)]),
     "b2lz4_compress_device": (_sz, [_vp, _vp, _sz, _vp, _sz]),

@@ -120,25 +120,13 @@ void do_decompress(FILE* in, FILE* out, bool all_frames) {
             break;
         }
         const bool skippable = magic != 0x184D2204u;
-        // ---- one frame through LZ4F_decompress (a skippable frame is consumed inside it and the state returns to "header")
+        // ---- one frame through LZ4F_decompress until it returns 0 (a skippable frame is consumed inside it and ends with 0 too)
         size_t hint = 1;
         while (hint != 0) {
             if (rd.avail() == 0) { rd.refill(); if (rd.avail() == 0) {
-                if (skippable) break;                                                           // ended inside / right after a skippable frame
+                if (skippable) die("skippable frame: truncated");
                 die("decompress: stream ended before EndMark"); } }                            // Conduit.hsc:689
             size_t ssz = rd.avail(), dsz = obuf.size();
-            if (skippable) {                                                                    // feed exactly the skippable frame: 8 + size bytes
-                if (!rd.fill(8)) die("skippable frame: truncated header");
-                uint64_t left = 8ull + le32(rd.ptr() + 4);
-                while (left) {
-                    if (rd.avail() == 0) { rd.refill(); if (rd.avail() == 0) die("skippable frame: truncated"); }
-                    size_t k = (size_t)(left < rd.avail() ? left : rd.avail()), one = k, z = 0;
-                    check(LZ4F_decompress(d, nullptr, &z, rd.ptr(), &one, nullptr));
-                    rd.consume(one); left -= one;
-                    if (one == 0) die("skippable frame: no progress");
-                }
-                break;
-            }
             hint = check(LZ4F_decompress(d, obuf.data(), &dsz, rd.ptr(), &ssz, nullptr));
             put(out, obuf.data(), dsz);
             rd.consume(ssz);

@@ -33,6 +33,8 @@ def bs_chunks_of(n, bs):
     """bsChunksOf (Conduit.hsc:428-433): split into chunks of n bytes, last one shorter."""
     if n < 1:
         raise ValueError(f"bsChunksOf: chunkSize < 1: {n}")
+    if len(bs) <= n:                     # first equation of the reference: [bs], also for the empty ByteString
+        return [bs]
     return [bs[i:i + n] for i in range(0, len(bs), n)]
 
 
@@ -147,11 +149,10 @@ class Codec:
         if len(frame) < 5:
             raise Lz4FrameError("decompress: not enough bytes for header")      # Conduit.hsc:615-616
         info, _ = frame_header_parse(frame)
-        if max_out is None:
+        if max_out is None:                 # blocks in the frame (host walk over the header words) x block size
+            max_out = _check(self.lib, self.lib.b2lz4_decompress_bound(frame, len(frame)))
             if info.has_content_size:
-                max_out = info.content_size
-            else:                           # upper bound: every block full (LZ4 expands by at most 255x)
-                max_out = min(len(frame) * 255 + 64, (len(frame) // 5 + 1) * info.block_size)
+                max_out = min(max_out, info.content_size) if info.content_size else max_out
         out = C.create_string_buffer(max(1, max_out))
         r, consumed = self.decompress_host_ptr(frame, len(frame), out, max_out)
         return out.raw[:r], consumed

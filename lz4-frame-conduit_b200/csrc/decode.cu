@@ -228,7 +228,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
         if ((mode & SCAN_OVERLAP_WALK) && s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) {
             // the walk is left to the decoder kernel, which runs it next to the decoding warps (walk_blocks below)
             s.walk_pending = 1;
-            walk[0] = 0; walk[1] = 0;
+            walk[0] = 0; walk[1] = 0; walk[2] = 0;
             *fi = s;
             return;
         }
@@ -470,7 +470,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
                 const uint32_t token = sp[ip];
                 uint32_t ll = token >> 4, ml = (token & 15u) + 4u, lit = ip + 1u;
                 bool more = false;
-                if (ll == 15u) { const uint32_t e = sp[lit++]; ll += e; more = (e == 255u); }
+                if (ll == 15u) { const uint32_t e = sp[lit++]; ll += e; more = (e >= 240u); }   // ll stays below 256: 8 bits in the packed form
                 uint32_t q = lit + ll;
                 const uint32_t offset = (uint32_t)sp[q] | ((uint32_t)sp[q + 1] << 8);
                 q += 2u;
@@ -478,7 +478,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
                 if (!more) {
                     const uint32_t mop = op + ll;
                     if (offset == 0u || offset > mop + reach) { err = E_decompressionFailed; break; }   // lz4.c:1977
-                    if (lane == n) { my_a = lit | (ll << 22); my_b = offset | (ml << 16); }
+                    if (lane == n) { my_a = lit | (ll << 24); my_b = offset | (ml << 16); }   // lit < 2^24: legacy blocks reach 8 MB + 32 KB
                     ip = q;
                     op = mop + ml;
                     continue;
@@ -528,7 +528,7 @@ __device__ __noinline__ uint32_t decode_piece(Cursor& c, bool ends_block)
             if (piece_ends) { ++n; finished = true; break; }
         }
         if (err) break;                                                     // nothing of a bad batch is copied
-        if (my_packed) { my_lit = my_a & 0x3FFFFFu; my_ll = my_a >> 22; my_off = my_b & 0xFFFFu; my_ml = my_b >> 16; }
+        if (my_packed) { my_lit = my_a & 0xFFFFFFu; my_ll = my_a >> 24; my_off = my_b & 0xFFFFu; my_ml = my_b >> 16; }
         // output position of sequence i = op0 + sum of the sizes of the sequences before it
         uint32_t my_op = my_op_fast;
         if (!fast_batch) {
@@ -617,11 +617,14 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* _
     // walk_pending: the block headers have not been walked yet (plain frame, no index).  Warp 0 of CTA 0 does it now, with
     // one thread, publishing every block as it is found; all other warps start decoding published blocks at once, so the
     // serial hops through the headers (one DRAM round trip each) hide behind the decoding instead of preceding it.
-    // CTA 0 is resident from the start of the grid, and the walker never waits for anybody: no deadlock.
+    // The walker is whichever warp draws walk[2] first — a warp that is running, whatever order the CTAs of the grid
+    // are dispatched in — and it never waits for anybody: no deadlock.
     const bool pending = fi->walk_pending != 0;
     const uint32_t block_size = fi->block_size;
     const bool linked = !fi->desc.block_independent;
-    if (pending && blockIdx.x == 0 && threadIdx.x < 32u) {
+    uint32_t walker = 0;
+    if (pending) { if (lane == 0) walker = atomicAdd(walk + 2, 1u) == 0u ? 1u : 0u; walker = __shfl_sync(FULL_MASK, walker, 0); }
+    if (walker) {
         if (lane == 0) {
             FrameIndex s = *fi;
             walk_blocks(src, n_src, mode, s, blocks, cap_tables, pieces, cap_tables, chains, stored_list, walk);

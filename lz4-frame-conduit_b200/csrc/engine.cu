@@ -51,7 +51,7 @@ struct Small {                 // small device-side state, mirrored to pinned ho
     EncodeResult eres;
     XxhState xxh;
     uint32_t ticket_dec, ticket_enc, crc_bad, hash_out;
-    uint32_t walk[2];          // decoder-side block walk: chains published so far, done flag
+    uint32_t walk[4];          // decoder-side block walk: chains published so far, done flag, walker ticket
 };
 
 }  // namespace
@@ -766,6 +766,28 @@ static bool host_scan(const uint8_t* src, size_t n, bool use_index, HostFrame& f
         }
     }
     return true;
+}
+
+// Upper bound of the decoded size of the first frame in src[0, n): its blocks are counted by walking the 4-byte header
+// words on the host (what LZ4F_decompress learns block by block, lz4frame.c:1470-1500), every block taken as full.  A
+// truncated frame is bounded by the blocks that are there (decoding it reports ERROR_noEndMark).  Host only, no GPU.
+size_t b2lz4_decompress_bound(const void* src_, size_t n) {
+    if (!src_) return err_code(E_GENERIC);
+    const uint8_t* src = (const uint8_t*)src_;
+    FrameDesc d{};
+    const Err e = header_parse(src, n, d);
+    if (e != OK) return err_code(e);
+    const size_t bs = block_size_of(d.block_size_id);
+    const uint32_t bc = d.block_checksum ? 4u : 0u;
+    size_t ip = d.header_size, nb = 0;
+    while (n - ip >= 4) {
+        const uint32_t cs = ld_le32(src + ip) & 0x7FFFFFFFu;
+        if (cs == 0) break;
+        ++nb;
+        if (cs > bs || n - ip - 4 < (size_t)cs + bc) break;       // malformed / truncated: the decoder reports it
+        ip += 4 + (size_t)cs + bc;
+    }
+    return nb * bs;
 }
 
 static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const HostFrame& f, size_t per_group,

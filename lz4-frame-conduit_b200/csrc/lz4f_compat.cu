@@ -500,7 +500,9 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
         const size_t sk = d->pre_acked < srcSize ? d->pre_acked : srcSize;
         consumed += sk; d->pre_acked -= sk;
     }
+    bool skipped = false;
     for (;;) {
+        if (skipped) break;
         if (d->out_pos < d->out_len) {                                               // hand out decoded bytes first
             const size_t k = std::min(dstCap - produced, d->out_len - d->out_pos);
             { Span sp(d->tr.t_out); memcpy(dst + produced, d->out.p + d->out_pos, k); }
@@ -529,7 +531,7 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
             const size_t k = std::min(avail, want - d->hdr_len);
             memcpy(d->hdr + d->hdr_len, src + consumed, k); d->hdr_len += (uint32_t)k; consumed += k;
             if (d->hdr_len >= 5 && (ld_le32(d->hdr) & 0xFFFFFFF0u) == MAGIC_SKIP_LO) {
-                if (d->hdr_len == 8) { d->skip_left = ld_le32(d->hdr + 4); d->hdr_len = 0; d->stage = DS_SKIP_DATA; }
+                if (d->hdr_len == 8) { d->skip_left = ld_le32(d->hdr + 4); d->hdr_len = 0; d->stage = DS_SKIP_DATA; if (d->skip_left == 0) skipped = true; }
             } else if (d->hdr_len >= 5 && ld_le32(d->hdr) == MAGIC_FRAME && d->hdr_len == header_size_from_flg(d->hdr[4])) {
                 size_t r = header_done(d);
                 if (b2lz4_is_error(r)) return fail(r);
@@ -539,7 +541,7 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
         case DS_SKIP_DATA: {                                                         // lz4frame.c:1756-1801
             const size_t k = (size_t)std::min<uint64_t>(avail, d->skip_left);
             consumed += k; d->skip_left -= k;
-            if (d->skip_left == 0) d->stage = DS_HEADER;                             // a skippable frame is not "a frame": keep going
+            if (d->skip_left == 0) skipped = true;                                   // frame boundary: reset and return 0 (lz4frame.c:1789-1799)
             break;
         }
         case DS_BLOCK_HEADER: {
@@ -587,6 +589,11 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
         }
         default: break;
         }
+    }
+    if (skipped) {                                                                   // a skippable frame ends like any frame: context reset, 0
+        *srcSizePtr = consumed; *dstSizePtr = produced;
+        dctx_reset(d);
+        return 0;
     }
     const bool pending = d->out_pos < d->out_len || (d->flight && d->stage == DS_DONE);
     if (d->stage == DS_DONE && !pending) {                                           // everything is decoded: the frame's own checks

@@ -95,6 +95,29 @@ def test_cli_all_frames_like_lz4_d(lz4_cli, gen, tmp_path):
     assert p.stdout == a and b"undecodable" in p.stderr
 
 
+def test_cli_legacy_low_ratio_blocks_over_4mib(lz4_cli):
+    """`lz4 -l` blocks are 8 MB and, at a ratio near 1.3, their COMPRESSED size exceeds 4 MiB: block-relative offsets in the
+    decoder need more than 22 bits there (the serial short path once packed them into 22).  Input: random 200-byte runs
+    interleaved with short repeats, so every batch mixes long literal runs (general path) with short sequences."""
+    import random
+    rnd = random.Random(11)
+    parts, total = [], 0
+    while total < (20 << 20):
+        lit = rnd.randbytes(rnd.randrange(150, 260))
+        parts.append(lit)
+        rep = lit[rnd.randrange(0, 100):][:rnd.randrange(8, 60)]
+        for _ in range(rnd.randrange(1, 4)):
+            parts.append(rep); parts.append(rnd.randbytes(rnd.randrange(1, 9)))
+        total += len(lit) + 4 * len(rep)
+    data = b"".join(parts)
+    frame = run([lz4_cli, "-c", "-l"], data).stdout
+    assert frame[:4] == struct.pack("<I", 0x184C2102)
+    first = struct.unpack_from("<I", frame, 4)[0]
+    assert first > (4 << 20), f"first legacy block is only {first} B compressed"
+    assert run([lz4_cli, "-d", "-c"], frame).stdout == data
+    assert run([CLI, "-d", "--all-frames"], frame).stdout == data
+
+
 def test_cli_errors_match_the_conduit(lz4_cli):
     frame = run([lz4_cli, "-c"], b"hellohellohellohello" * 1000).stdout
     p = run([CLI, "-d"], frame[:-6], ok=False)

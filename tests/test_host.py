@@ -43,7 +43,8 @@ def test_error_names_match_reference_library(pkg, ref):
 def test_bs_chunks_of(pkg):
     # the only literal known-answer of the reference package (test/Main.hs:56-58)
     assert pkg.bs_chunks_of(3, b"abc123def4567") == [b"abc", b"123", b"def", b"456", b"7"]
-    assert pkg.bs_chunks_of(5, b"") == []
+    assert pkg.bs_chunks_of(5, b"") == [b""]            # `BS.length bs <= chunkSize = [bs]` comes first (Conduit.hsc:428-433)
+    assert pkg.bs_chunks_of(5, b"abc") == [b"abc"] and pkg.bs_chunks_of(3, b"abc") == [b"abc"]
     with pytest.raises(ValueError):
         pkg.bs_chunks_of(0, b"x")
 
