@@ -1,6 +1,6 @@
 // common.cuh — device helpers shared by the sm_100a kernels (byte access, warp copies, XXH32).
 #pragma once
-#include <cuda_runtime.h>
+#include "b2_cuda.h"
 #include <stdint.h>
 #include "device_types.h"
 
@@ -10,7 +10,11 @@ constexpr unsigned FULL_MASK = 0xffffffffu;
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
+#if B2_PTX
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+#else
+__device__ __forceinline__ void prefetch_l1(const void*) {}
+#endif
 
 // 4 bytes at an arbitrary address, little endian.  Touches only the aligned words that contain them.
 __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {

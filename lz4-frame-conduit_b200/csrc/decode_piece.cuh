@@ -1,0 +1,541 @@
+// decode_piece.cuh — the warp-level LZ4 sequence decoder shared by decode.cu (one warp per independent piece) and
+// decode_df.cu (dataflow mode: pieces of foreign / linked blocks whose matches wait for bytes other warps produce).
+// Replaces LZ4_decompress_generic (lz4/lib/lz4.c:1653-2068); acceptance rules mirror its safe loop (lz4.c:1844-2055).
+#pragma once
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------------
+// sequence decoder: one warp per chain, pieces in order.
+// All lanes keep identical parse state (uniform control flow); literal and match copies are spread
+// over the 32 lanes.  Acceptance rules mirror the reference decoder's safe loop (lz4.c:1844-2055).
+// ------------------------------------------------------------------------------------------------
+struct Cursor {            // what the warp knows about the piece it is decoding (all offsets 32-bit, block-relative)
+    const uint8_t* sp;     // first compressed byte of the owning block
+    uint8_t* dp;           // first output byte of the owning block
+    uint32_t ip, iend;     // current / end of this piece's compressed bytes
+    uint32_t iend_blk;     // end of the owning block's compressed bytes (reference's `iend`)
+    uint32_t op, oend;     // current output position / output limit of the owning block (reference's `oend`)
+    uint32_t opiece_end;   // exact end of this piece's output (PIECE_EXACT) or == oend
+    uint8_t* win;          // this warp's shared memory: 272-byte window of the compressed stream + 5 link tables of 256 bytes
+    const uint8_t* src_end;// end of the compressed buffer (words that start at or after it are not read)
+    uint32_t p_dst, p_off, p_ml;  // DEC_PAUSED: a huge overlapping match the caller fills (dp + p_dst, offset, length)
+    bool p_done;           // ... and whether the piece ended with it
+    uint32_t reach;        // a match at output position m may reach back `m + reach` bytes (mod 2^32):
+                           // independent piece: -piece_start;  linked: bytes of earlier output in front of the block
+    // dataflow mode (decode_df.cu): bytes below piece_lo are written by OTHER warps; bit i of `bits` = output byte i of
+    // the destination buffer is final.  abs0 = offset of the owning block's first output byte in that buffer.
+    uint32_t* bits;
+    int64_t abs0;
+    uint32_t piece_lo;
+};
+
+// ---- dataflow helpers: the "final bytes" bitmap.  A writer stores its bytes, fences, then sets their bits; a reader
+// loads the bits with acquire semantics and only then the bytes (past L1, which is not coherent between SMs).
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
+#if B2_PTX
+    uint32_t v; asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
+#else
+    return __atomic_load_n(p, __ATOMIC_ACQUIRE);
+#endif
+}
+// all of the bytes [a, b) final?  Positions below 0 are history in front of the buffer: final by construction.
+__device__ __forceinline__ bool bits_ready(const uint32_t* bits, int64_t a, int64_t b) {
+    if (a < 0) a = 0;
+    if (b <= a) return true;
+    const uint64_t w0 = (uint64_t)a >> 5, w1 = (uint64_t)(b - 1) >> 5;
+    const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
+    if (w0 == w1) { const uint32_t m = m0 & m1; return (ld_acquire(bits + w0) & m) == m; }
+    if ((ld_acquire(bits + w0) & m0) != m0) return false;
+    for (uint64_t w = w0 + 1; w < w1; ++w) if (ld_acquire(bits + w) != 0xFFFFFFFFu) return false;
+    return (ld_acquire(bits + w1) & m1) == m1;
+}
+// the same question asked by the whole warp about a long range (uniform answer)
+__device__ __forceinline__ bool bits_ready_warp(const uint32_t* bits, int64_t a, int64_t b, uint32_t lane) {
+    if (a < 0) a = 0;
+    if (b <= a) return true;
+    const uint64_t w0 = (uint64_t)a >> 5, w1 = (uint64_t)(b - 1) >> 5;
+    const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
+    bool ok = true;
+    for (uint64_t w = w0 + lane; w <= w1 && ok; w += 32) {
+        uint32_t m = 0xFFFFFFFFu;
+        if (w == w0) m &= m0;
+        if (w == w1) m &= m1;
+        ok = (ld_acquire(bits + w) & m) == m;
+    }
+    return __all_sync(FULL_MASK, ok);
+}
+// marks [a, b) final; the caller has fenced its stores.  One lane, short ranges (a few words).
+__device__ __forceinline__ void bits_mark(uint32_t* bits, uint64_t a, uint64_t b) {
+    if (b <= a) return;
+    const uint64_t w0 = a >> 5, w1 = (b - 1) >> 5;
+    const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
+    if (w0 == w1) { atomicOr(bits + w0, m0 & m1); return; }
+    atomicOr(bits + w0, m0);
+    for (uint64_t w = w0 + 1; w < w1; ++w) atomicOr(bits + w, 0xFFFFFFFFu);
+    atomicOr(bits + w1, m1);
+}
+// ... by the whole warp, any length (every lane has fenced its stores and the warp has synchronised)
+__device__ __forceinline__ void bits_mark_warp(uint32_t* bits, uint64_t a, uint64_t b, uint32_t lane) {
+    if (b <= a) return;
+    const uint64_t w0 = a >> 5, w1 = (b - 1) >> 5;
+    const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
+    for (uint64_t w = w0 + lane; w <= w1; w += 32) {
+        uint32_t m = 0xFFFFFFFFu;
+        if (w == w0) m &= m0;
+        if (w == w1) m &= m1;
+        atomicOr(bits + w, m);
+    }
+}
+// copies whose source was written by another SM read it past L1
+__device__ __forceinline__ void lane_copy_cg(uint8_t* d, const uint8_t* s, uint32_t n) {
+    uint32_t k = 0;
+    for (; k + 4 <= n; k += 4) {
+        uint8_t a = __ldcg(s + k), b = __ldcg(s + k + 1), c = __ldcg(s + k + 2), e = __ldcg(s + k + 3);
+        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
+    }
+    for (; k < n; ++k) d[k] = __ldcg(s + k);
+}
+__device__ __forceinline__ void lane_match_cg(uint8_t* d, uint32_t off, uint32_t n) {
+    const uint8_t* s = d - off;
+    uint32_t r = 0;
+    for (uint32_t k = 0; k < n; ++k) { d[k] = __ldcg(s + r); r = (r + 1 == off) ? 0u : r + 1; }
+}
+__device__ __forceinline__ void group_copy_cg(uint8_t* dst, const uint8_t* src, uint64_t n, uint32_t tid, uint32_t nthreads) {
+    uint32_t head = (uint32_t)((4u - ((uintptr_t)dst & 3u)) & 3u);
+    if (head > n) head = (uint32_t)n;
+    if (tid < head) dst[tid] = __ldcg(src + tid);
+    dst += head; src += head; n -= head;
+    const uint64_t nw = n >> 2;
+    const uint32_t sh = (uint32_t)((uintptr_t)src & 3u) * 8u;
+    const uint32_t* sw = (const uint32_t*)((uintptr_t)src & ~(uintptr_t)3);
+    uint32_t* dw = (uint32_t*)dst;
+    if (sh == 0) { for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = __ldcg(sw + i); }
+    else { for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = __funnelshift_r(__ldcg(sw + i), __ldcg(sw + i + 1), sh); }
+    const uint64_t done = nw << 2;
+    if (tid < (uint32_t)(n - done)) dst[done + tid] = __ldcg(src + done + tid);
+}
+
+// Per-lane byte copy of n bytes; loads are batched four at a time ahead of the stores so that a lane
+// keeps several loads in flight.  `s` must not overlap the destination (callers guarantee it).
+__device__ __forceinline__ void lane_copy(uint8_t* d, const uint8_t* s, uint32_t n) {
+    uint32_t k = 0;
+    for (; k + 4 <= n; k += 4) {
+        uint8_t a = s[k], b = s[k + 1], c = s[k + 2], e = s[k + 3];
+        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
+    }
+    for (; k < n; ++k) d[k] = s[k];
+}
+
+// Per-lane match copy: replicates the FINAL window [d - off, d) with period `off` (off >= n: plain copy).
+// All loads come from the window, never from bytes this call writes, so they do not wait on the stores.
+__device__ __forceinline__ void lane_match(uint8_t* d, uint32_t off, uint32_t n) {
+    const uint8_t* s = d - off;
+    uint32_t r = 0, k = 0;
+    for (; k + 4 <= n; k += 4) {
+        uint8_t a = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        uint8_t b = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        uint8_t c = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        uint8_t e = s[r]; r = (r + 1 == off) ? 0u : r + 1;
+        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
+    }
+    for (; k < n; ++k) { d[k] = s[r]; r = (r + 1 == off) ? 0u : r + 1; }
+}
+
+// Warp-cooperative match copy (long matches): the source window [d - off, d) is final.
+//   off >= ml            plain copy
+//   16 % off == 0        (run-length style: 1, 2, 4, 8, 16) every aligned 16-byte chunk of the run holds the same
+//                        pattern, built once per lane in registers and streamed out with 16-byte stores
+//   other overlaps       the first bytes are replicated directly, then the valid region doubles: each round copies a
+//                        whole number of periods from what is already there (non-overlapping, so the wide copy applies)
+// (rare paths are kept out of line so that their registers do not weigh on the sequence loop)
+__device__ __forceinline__ void warp_match_overlap(uint8_t* d, uint32_t offset, uint64_t ml, uint32_t lane) {
+    const uint8_t* m = d - offset;
+    if ((16u % offset) == 0u && ml >= 64u) {
+        const uint32_t head = (uint32_t)((16u - ((uintptr_t)d & 15u)) & 15u);
+        if (lane < head) d[lane] = m[lane % offset];
+        uint32_t pw[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t v = 0;
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) v |= (uint32_t)m[(head + 4u * j + k) % offset] << (8 * k);
+            pw[j] = v;
+        }
+        __syncwarp();
+        const uint4 P = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+        uint4* d4 = (uint4*)(d + head);
+        const uint64_t nq = (ml - head) >> 4;
+        #pragma unroll 4
+        for (uint64_t q = lane; q < nq; q += 32) d4[q] = P;
+        const uint64_t done = head + (nq << 4);
+        if (lane < (uint32_t)(ml - done)) d[done + lane] = m[(done + lane) % offset];
+        return;
+    }
+    // direct replication of the first bytes (enough for the doubling rounds to use wide copies soon)
+    uint64_t done = ml < 256u ? ml : 256u;
+    {
+        uint32_t r = lane % offset; const uint32_t step = 32u % offset;
+        for (uint32_t i = lane; i < (uint32_t)done; i += 32) { d[i] = m[r]; r += step; if (r >= offset) r -= offset; }
+    }
+    while (done < ml) {
+        __syncwarp();
+        const uint64_t L = ((offset + done) / offset) * offset;         // whole periods available behind d + done
+        const uint64_t cnt = (ml - done) < L ? (ml - done) : L;
+        group_copy(d + done, d + done - L, cnt, lane, 32);
+        done += cnt;
+    }
+}
+
+// table entries are read past L1: in walk_pending mode another CTA of this very kernel has just written them
+template <typename T>
+__device__ __forceinline__ T ld_cg(const T* p) {
+    static_assert(sizeof(T) % 16 == 0, "16-byte multiples only");
+    T v;
+    #pragma unroll
+    for (uint32_t i = 0; i < sizeof(T) / 16; ++i) ((uint4*)&v)[i] = __ldcg((const uint4*)p + i);
+    return v;
+}
+
+constexpr uint32_t DEC_PAUSED = 0xFFFFFFFEu;   // decode_piece: stopped in front of a huge overlapping match (see Cursor::p_*)
+constexpr uint32_t HUGE_MATCH = 512u;          // overlapping matches at least this long are filled outside the sequence loop
+constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
+#ifndef B2_DEC_PREFETCH
+#define B2_DEC_PREFETCH 2      // 128-byte lines of the compressed stream requested ahead at every window refill
+#endif
+#ifndef B2_DEC_LANE_CAP
+#define B2_DEC_LANE_CAP 24
+#endif
+constexpr uint32_t LANE_CAP = B2_DEC_LANE_CAP;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
+
+// Decodes one piece.  The warp first WALKS up to 32 sequences (uniform control flow: every lane follows the
+// token chain, lane i keeps the fields of sequence i), then copies them lane-parallel: literals of all 32
+// sequences at once, then matches in rounds — a match may run as soon as every byte it reads is final, i.e.
+// lies below the destination of the first match still pending (all literals are already in place).
+// The walk has a short path for the common sequence (both nibbles < 15, far from every limit) whose only
+// check is the offset; everything else takes the general path with the reference's acceptance rules.
+// returns 0 or an Err; c.op is advanced
+template <bool DF>
+__device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
+{
+    const uint32_t lane = lane_id();
+    const uint8_t* __restrict__ sp = c.sp;
+    uint8_t* dp = c.dp;
+    uint32_t ip = c.ip, op = c.op;
+    const uint32_t iend = c.iend_blk, pend = c.iend, oend = c.oend, opend = c.opiece_end, reach = c.reach;
+    // short path (lengths with at most one extension byte) allowed while  ip + 288 <= pend  and
+    // op + 560 <= min(oend, opend): inside that region none of the general path's limit checks can fire
+    // dataflow pieces are short (about 1 KB of the stream): their own end only bounds WHICH tokens are theirs; the limit
+    // checks the short path skips are about the end of the BLOCK (input) and of its output window
+    uint32_t i_fast = DF ? (iend >= 288u ? (pend < iend - 287u ? pend : iend - 287u) : 0u) : (pend >= 288u ? pend - 287u : 0u);
+    const uint32_t olim = oend < opend ? oend : opend;
+    uint32_t o_fast = DF ? (oend >= 560u ? (opend < oend - 559u ? opend : oend - 559u) : 0u) : (olim >= 560u ? olim - 559u : 0u);
+    const uint32_t piece_lo = DF ? c.piece_lo : 0u;
+    uint32_t* const bits = DF ? c.bits : nullptr;
+    const int64_t abs0 = DF ? c.abs0 : 0;
+    asm volatile("" : "+r"(i_fast), "+r"(o_fast));                          // keep them in registers (no re-derivation per sequence)
+    uint32_t err = 0;
+    if (pend == ip) return E_decompressionFailed;                           // empty input (lz4.c:1702)
+    // ---- lane-parallel token walk (the common case).  128 consecutive bytes of the stream are examined at once:
+    // every lane computes, for 4 byte positions, where the next token would be IF a token started there (one
+    // shared-memory byte, two with an extension byte).  Squaring that link table four times (T1, T2, T4, T8, T16)
+    // lets lane i jump straight to the i-th token after the known entry point, so 32 sequences are located in a
+    // handful of instructions instead of a 32-step dependent chain of loads.  Anything unusual (a second extension
+    // byte, a literal run that leaves the window, the last 288 input / 560 output bytes of the piece) is marked
+    // WSTOP and goes through the general path below, which carries every acceptance rule of the reference.
+    uint8_t* const win = c.win;
+    uint8_t* const T1 = win + 272, * const T2 = T1 + 256, * const T4 = T2 + 256, * const T8 = T4 + 256, * const T16 = T8 + 256;
+    int32_t wb = 0; bool win_ok = false;                                    // window = stream bytes [wb, wb + 256)
+    bool finished = false, paused = false;
+    while (!finished) {
+        if (DF && ip >= pend && !ends_block) {                              // the piece's last sequence took the short path
+            if (ip != pend || op != opend) err = E_decompressionFailed;
+            break;
+        }
+        uint32_t my_a = 0, my_b = 0, my_lit = 0, my_ll = 0, my_ml = 0, my_off = 1;
+        bool my_packed = true, fast_batch = false;
+        uint32_t my_op_fast = 0;
+        const uint32_t op0 = op;
+        uint32_t n = 0;
+        if (ip < i_fast && op < o_fast) {
+            // gather up to 32 sequences, refilling the window as often as needed: lanes n.. take the tokens that follow `tip`
+            uint32_t tip = ip, my_tok = 0, my_nxt = 0, ll = 0, ml = 0, off = 1, lit = 0;
+            while (tip < i_fast) {
+                if (!win_ok || (uint32_t)((int32_t)tip - wb) >= 128u) {
+                    // (re)fill the window; its base is 4-byte aligned in memory so that every lane moves whole words
+                    wb = (int32_t)tip - (int32_t)((uintptr_t)(sp + tip) & 3u);
+                    const uint8_t* g = sp + wb;
+                    __syncwarp();
+#if B2_DEC_PREFETCH
+                    // the lines the NEXT refills (and this batch's literal copies) will want: a warp reads its stream strictly
+                    // forward, one dependent DRAM round trip per window if nobody asks ahead
+                    if (lane < (uint32_t)B2_DEC_PREFETCH && g + 256u + 128u * lane < c.src_end) prefetch_l1(g + 256u + 128u * lane);
+#endif
+                    const uint32_t w0 = (g + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 4u * lane) : 0u;
+                    const uint32_t w1 = (g + 128u + 4u * lane < c.src_end) ? *(const uint32_t*)(g + 128u + 4u * lane) : 0u;
+                    ((uint32_t*)win)[lane] = w0; ((uint32_t*)win)[32u + lane] = w1;
+                    if (lane < 4u) ((uint32_t*)win)[64u + lane] = 0u;
+                    __syncwarp();
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t p = 32u * k + lane;
+                        const uint32_t t = win[p];
+                        uint32_t l2 = t >> 4, q = p + 1u;
+                        bool stop = (wb + (int32_t)p) >= (int32_t)i_fast;
+                        if (l2 == 15u) { const uint32_t e = win[q]; l2 += e; ++q; stop |= (e == 255u); }
+                        q += l2;
+                        if (q > 250u) { stop = true; q = 250u; }
+                        q += 2u;
+                        if ((t & 15u) == 15u) { const uint32_t e = win[q]; ++q; stop |= (e == 255u); }
+                        T1[p] = (uint8_t)(stop ? WSTOP : q);
+                    }
+                    __syncwarp();
+                    #define B2_SQUARE(TA, TB) { uint8_t r0 = TA[TA[lane]], r1 = TA[TA[32u + lane]], r2 = TA[TA[64u + lane]], r3 = TA[TA[96u + lane]]; \
+                        TB[lane] = r0; TB[32u + lane] = r1; TB[64u + lane] = r2; TB[96u + lane] = r3; __syncwarp(); }
+                    B2_SQUARE(T1, T2) B2_SQUARE(T2, T4) B2_SQUARE(T4, T8) B2_SQUARE(T8, T16)
+                    #undef B2_SQUARE
+                    win_ok = true;
+                }
+                // lane n + i: the i-th token after `tip`
+                const uint32_t kx = lane - n;                                   // lanes below n already hold a sequence
+                uint32_t x = tip - (uint32_t)wb;
+                if (kx & 1u) x = T1[x];
+                if (kx & 2u) x = T2[x];
+                if (kx & 4u) x = T4[x];
+                if (kx & 8u) x = T8[x];
+                if (kx & 16u) x = T16[x];
+                const uint32_t nxt = T1[x];                                     // entries 128..255 are identity: harmless for x >= 128
+                const bool have = lane >= n && x < 128u && nxt != WSTOP;
+                if (have) {
+                    const uint32_t t = win[x];
+                    ll = t >> 4; lit = x + 1u;
+                    if (ll == 15u) { ll += win[lit]; ++lit; }
+                    const uint32_t q = lit + ll;
+                    off = (uint32_t)win[q] | ((uint32_t)win[q + 1u] << 8);
+                    ml = (t & 15u) + 4u;
+                    if (ml == 19u) ml += win[q + 2u];
+                    lit = (uint32_t)(wb + (int32_t)lit);
+                    my_tok = (uint32_t)(wb + (int32_t)x); my_nxt = (uint32_t)(wb + (int32_t)nxt);
+                }
+                const uint32_t nh = (uint32_t)__popc(__ballot_sync(FULL_MASK, have));     // `have` lanes form a run that starts at lane n
+                if (nh == 0u) break;
+                n += nh;
+                tip = __shfl_sync(FULL_MASK, my_nxt, n - 1u);
+                if (n == 32u) break;
+            }
+            if (n) {
+                const uint32_t sz = (lane < n) ? ll + ml : 0u;
+                uint32_t run = sz;
+                #pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, run, d); if ((int)lane >= d) run += y; }
+                const uint32_t seq_op = op0 + run - sz;                         // where this lane's sequence starts
+                const bool fits = lane < n && seq_op < o_fast;                  // a prefix (lane 0 always fits)
+                const uint32_t nf = (uint32_t)__popc(__ballot_sync(FULL_MASK, fits));
+                const bool bad = lane < nf && (off == 0u || off > seq_op + ll + reach);              // lz4.c:1977
+                if (__any_sync(FULL_MASK, bad)) { err = E_decompressionFailed; break; }
+                // entry point and output position after the nf sequences taken
+                const uint32_t nx_ip = __shfl_sync(FULL_MASK, my_tok, nf & 31u);
+                const uint32_t nx_op = __shfl_sync(FULL_MASK, nf < 32u ? seq_op : seq_op + sz, nf < 32u ? nf : 31u);
+                ip = (nf < n) ? nx_ip : tip; op = nx_op;
+                n = nf;
+                my_lit = lit; my_ll = ll; my_ml = ml; my_off = off; my_op_fast = seq_op;
+                if (lane >= n) { my_ll = 0; my_ml = 0; my_off = 1; }
+                my_packed = false; fast_batch = true;
+            }
+        }
+        if (n == 0)
+        for (; n < 32; ++n) {
+            if (DF && !ends_block && ip >= pend) break;                     // the piece's tokens are used up: copy what was gathered
+            if (ip < i_fast && op < o_fast) {
+                const uint32_t token = sp[ip];
+                uint32_t ll = token >> 4, ml = (token & 15u) + 4u, lit = ip + 1u;
+                bool more = false;
+                if (ll == 15u) { const uint32_t e = sp[lit++]; ll += e; more = (e >= 240u); }   // ll stays below 256: 8 bits in the packed form
+                uint32_t q = lit + ll;
+                const uint32_t offset = (uint32_t)sp[q] | ((uint32_t)sp[q + 1] << 8);
+                q += 2u;
+                if (ml == 19u) { const uint32_t e = sp[q++]; ml += e; more |= (e == 255u); }
+                if (!more) {
+                    const uint32_t mop = op + ll;
+                    if (offset == 0u || offset > mop + reach) { err = E_decompressionFailed; break; }   // lz4.c:1977
+                    if (lane == n) { my_a = lit | (ll << 24); my_b = offset | (ml << 16); }   // lit < 2^24: legacy blocks reach 8 MB + 32 KB
+                    ip = q;
+                    op = mop + ml;
+                    continue;
+                }
+            }
+            // ---- general path
+            if (ip >= pend) { err = E_decompressionFailed; break; }
+            const uint32_t token = sp[ip++];
+            uint32_t ll = token >> 4;
+            if (ll == 15u) {                                                // lz4.c:1882-1889
+                if (ip + 15u >= iend) { err = E_decompressionFailed; break; }
+                uint32_t sbyte;
+                do { sbyte = sp[ip++]; ll += sbyte; if (ip + 15u >= iend) break; } while (sbyte == 255u);
+            }
+            // last-sequence test (lz4.c:1906): not enough input for an offset + next token, or the
+            // literals reach the last 12 bytes of the block's output window.  (ll <= 255 * 4 MB: no overflow)
+            const bool last = (op + ll + 12u > oend) || (ip + ll + 8u > iend);
+            if (last) {
+                if (ip + ll != iend || op + ll > oend || !ends_block || op + ll > opend || iend != pend) {
+                    err = E_decompressionFailed; break;
+                }
+                if (lane == n) { my_lit = ip; my_ll = ll; my_ml = 0; my_packed = false; }
+                ip += ll; op += ll; ++n; finished = true;
+                break;
+            }
+            if (ip + ll + 2u > pend || op + ll > opend) { err = E_decompressionFailed; break; }
+            const uint32_t lit = ip;
+            ip += ll;
+            const uint32_t offset = (uint32_t)sp[ip] | ((uint32_t)sp[ip + 1] << 8);
+            ip += 2u;
+            uint32_t ml = token & 15u;
+            if (ml == 15u) {                                                // lz4.c:1967-1972
+                uint32_t sbyte; bool bad = false;
+                do { sbyte = sp[ip++]; ml += sbyte; if (ip + 4u >= iend) { bad = true; break; } } while (sbyte == 255u);
+                if (bad) { err = E_decompressionFailed; break; }
+            }
+            ml += 4u;
+            const uint32_t mop = op + ll;
+            if (offset == 0u || offset > mop + reach) { err = E_decompressionFailed; break; }           // lz4.c:1977
+            if ((uint64_t)mop + ml + 5u > oend || (uint64_t)mop + ml > opend) { err = E_decompressionFailed; break; } // lz4.c:2033-2035
+            const bool huge = ml >= HUGE_MATCH && offset < ml;             // run-length style: filled by the caller, out of this loop
+            if (lane == n) { my_lit = lit; my_ll = ll; my_ml = huge ? 0u : ml; my_off = offset; my_packed = false; }
+            op = mop + ml;
+            const bool piece_ends = (ip == pend && !ends_block);           // sub-block ends after a match
+            if (piece_ends && op != opend) { err = E_decompressionFailed; break; }
+            if (huge) { c.p_dst = mop; c.p_off = offset; c.p_ml = ml; c.p_done = piece_ends; paused = true; ++n; finished = true; break; }
+            if (piece_ends) { ++n; finished = true; break; }
+        }
+        if (err) break;                                                     // nothing of a bad batch is copied
+        if (my_packed) { my_lit = my_a & 0xFFFFFFu; my_ll = my_a >> 24; my_off = my_b & 0xFFFFu; my_ml = my_b >> 16; }
+        // output position of sequence i = op0 + sum of the sizes of the sequences before it
+        uint32_t my_op = my_op_fast;
+        if (!fast_batch) {
+            const uint32_t sz = my_ll + my_ml;
+            uint32_t x = sz;
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(FULL_MASK, x, d); if ((int)lane >= d) x += y; }
+            my_op = op0 + x - sz;
+        }
+
+        // ---- literals: lane i copies the literals of sequence i; long runs use the whole warp
+        {
+            const bool act = lane < n && my_ll != 0;
+            if (act && my_ll <= LANE_CAP) lane_copy(dp + my_op, sp + my_lit, my_ll);
+            uint32_t longm = __ballot_sync(FULL_MASK, act && my_ll > LANE_CAP);
+            const uint32_t longm0 = longm;
+            while (longm) {
+                const int j = __ffs(longm) - 1; longm &= longm - 1;
+                const uint32_t l = __shfl_sync(FULL_MASK, my_lit, j), o = __shfl_sync(FULL_MASK, my_op, j);
+                const uint32_t len = __shfl_sync(FULL_MASK, my_ll, j);
+                group_copy_small(dp + o, sp + l, len, lane, 32);
+            }
+            if (DF) {                                                       // literals never wait: publish them at once
+                __threadfence();
+                __syncwarp();
+                if (act && my_ll <= LANE_CAP) bits_mark(bits, (uint64_t)(abs0 + my_op), (uint64_t)(abs0 + my_op) + my_ll);
+                longm = longm0;
+                while (longm) {
+                    const int j = __ffs(longm) - 1; longm &= longm - 1;
+                    const uint32_t o = __shfl_sync(FULL_MASK, my_op, j), len = __shfl_sync(FULL_MASK, my_ll, j);
+                    bits_mark_warp(bits, (uint64_t)(abs0 + o), (uint64_t)(abs0 + o) + len, lane);
+                }
+            }
+        }
+        __syncwarp();
+        // ---- matches, in rounds
+        if (!DF) {
+            const uint32_t my_mop = my_op + my_ll;
+            // end of the bytes read, relative to the match destination: -(off) + min(ml, off)  (<= 0)
+            const int32_t my_need = (int32_t)(my_ml < my_off ? my_ml : my_off) - (int32_t)my_off;
+            uint32_t pending = __ballot_sync(FULL_MASK, lane < n && my_ml != 0);
+            while (pending) {
+                const int f = __ffs(pending) - 1;
+                const uint32_t W = __shfl_sync(FULL_MASK, my_mop, f);       // everything below W is final
+                const uint32_t ml_f = __shfl_sync(FULL_MASK, my_ml, f);
+                if (ml_f > LANE_CAP) {
+                    const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
+                    if (off_f >= ml_f) group_copy_small(dp + W, dp + W - off_f, ml_f, lane, 32);
+                    else {                                                  // overlapping, < HUGE_MATCH or from the short path: period replication
+                        const uint8_t* m = dp + W - off_f; uint32_t r = lane % off_f; const uint32_t step = 32u % off_f;
+                        for (uint32_t i = lane; i < ml_f; i += 32) { dp[W + i] = m[r]; r += step; if (r >= off_f) r -= off_f; }
+                    }
+                    pending &= ~(1u << f);
+                } else {
+                    const bool ready = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
+                                       ((int)lane == f || (int64_t)my_mop + my_need <= (int64_t)W);
+                    if (ready) { if (my_off >= my_ml) lane_copy(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match(dp + my_mop, my_off, my_ml); }
+                    pending &= ~__ballot_sync(FULL_MASK, ready);
+                }
+                __syncwarp();
+            }
+        } else {
+            // dataflow: a match whose source starts below piece_lo reads bytes other warps write; it goes when their bits
+            // are set.  Inside the piece the watermark rule above still applies (and costs no memory traffic).
+            const uint32_t my_mop = my_op + my_ll;
+            const uint32_t my_span = my_ml < my_off ? my_ml : my_off;       // bytes of the source window that are read
+            const int32_t my_need = (int32_t)my_span - (int32_t)my_off;
+            const bool my_ext = my_off > my_mop - piece_lo;                  // the source starts below piece_lo (also true for history / earlier blocks)
+            // external part of my source, in buffer coordinates: [xa, xb)
+            const int64_t xa = abs0 + (int64_t)my_mop - (int64_t)my_off;
+            const int64_t xe = xa + my_span, xl = abs0 + piece_lo;
+            const int64_t xb = xe < xl ? xe : xl;
+            bool ext_ok = !my_ext;
+            uint32_t pending = __ballot_sync(FULL_MASK, lane < n && my_ml != 0);
+            while (pending) {
+                const int f = __ffs(pending) - 1;
+                const uint32_t W = __shfl_sync(FULL_MASK, my_mop, f);       // everything of THIS piece below W is final
+                const uint32_t ml_f = __shfl_sync(FULL_MASK, my_ml, f);
+                const bool in_ok = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
+                                   ((int)lane == f || (int64_t)my_mop + my_need <= (int64_t)W);
+                if (in_ok && !ext_ok) ext_ok = bits_ready(bits, xa, xb);
+                const bool ready = in_ok && ext_ok;
+                if (ready) {
+                    if (my_ext) { if (my_off >= my_ml) lane_copy_cg(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match_cg(dp + my_mop, my_off, my_ml); }
+                    else        { if (my_off >= my_ml) lane_copy(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match(dp + my_mop, my_off, my_ml); }
+                }
+                const uint32_t rb = __ballot_sync(FULL_MASK, ready);
+                bool progressed = rb != 0u;
+                if (rb) {
+                    __threadfence();
+                    if (ready) bits_mark(bits, (uint64_t)(abs0 + my_mop), (uint64_t)(abs0 + my_mop) + my_ml);
+                    pending &= ~rb;
+                }
+                if (ml_f > LANE_CAP) {                                      // the first pending match is a long one: whole warp
+                    const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
+                    const bool ext_f = off_f > W - piece_lo;
+                    const uint32_t span_f = ml_f < off_f ? ml_f : off_f;
+                    bool ok = true;
+                    if (ext_f) {
+                        const int64_t a = abs0 + (int64_t)W - (int64_t)off_f, e = a + span_f, l = abs0 + piece_lo;
+                        ok = bits_ready_warp(bits, a, e < l ? e : l, lane);
+                    }
+                    if (ok) {
+                        __syncwarp();
+                        if (off_f >= ml_f) {
+                            if (ext_f) group_copy_cg(dp + W, dp + W - off_f, ml_f, lane, 32);
+                            else group_copy_small(dp + W, dp + W - off_f, ml_f, lane, 32);
+                        } else {                                            // overlapping: period replication from the final window
+                            const uint8_t* m = dp + W - off_f; uint32_t r = lane % off_f; const uint32_t step = 32u % off_f;
+                            for (uint32_t i = lane; i < ml_f; i += 32) { dp[W + i] = ext_f ? __ldcg(m + r) : m[r]; r += step; if (r >= off_f) r -= off_f; }
+                        }
+                        __threadfence();
+                        __syncwarp();
+                        bits_mark_warp(bits, (uint64_t)(abs0 + W), (uint64_t)(abs0 + W) + ml_f, lane);
+                        pending &= ~(1u << f);
+                        progressed = true;
+                    }
+                }
+                __syncwarp();
+                if (!progressed) __nanosleep(64);
+            }
+        }
+    }
+    c.ip = ip; c.op = op;
+    return err ? err : (paused ? DEC_PAUSED : 0u);
+}
+
+}  // namespace b2

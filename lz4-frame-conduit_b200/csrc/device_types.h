@@ -60,7 +60,34 @@ struct FrameIndex {
     uint32_t need_pieces;
     uint32_t n_stored;        // stored blocks listed for copy_stored_kernel
     uint32_t walk_pending;    // 1 = the serial walk over the block headers is left to the decoder kernel (2 = done there)
+    uint32_t df;              // 1 = decoded by the dataflow kernels (decode_df.cu): no side information, any block mode
+    uint32_t need_groups;     // dataflow workspace the scan wanted (groups of DF_G compressed bytes)
     FrameDesc desc;
+};
+
+// ---- dataflow decode (decode_df.cu)
+constexpr uint32_t DF_G = 1024u;            // compressed bytes per group = one chain table = (about) one piece
+constexpr uint32_t DF_LA = 96u;             // bytes behind a group its parse may look at (length runs longer than that: DF_SLOW)
+constexpr uint32_t DF_RUN = 64u;            // 255-bytes of one length field followed inside the table pass
+constexpr uint32_t DF_STORED_PIECE = 65536u;// a stored block is copied in pieces of this size
+struct DfHead { uint32_t exit, out; };      // chain from one position: where it leaves the group (kind in the top bits), bytes produced
+struct DfPiece { uint32_t block, tok, tok_end, out, out_end, flags, pad0, pad1; };   // block-relative token / output ranges
+struct DfState {
+    unsigned long long bad_key;             // min over failures of (block << 8 | Err); all ones = none
+    unsigned long long produced, total_out;
+    uint32_t n_pieces, ticket_links, ticket_decode, pad;
+};
+struct DfWork {                             // device workspaces of the dataflow path (all sized by the host from the scan's needs)
+    uint32_t* grp_base;                     // [blocks + 1] first group of every block
+    DfHead* heads;                          // [groups x DF_G]
+    uint2* ent;                             // [groups] (first token, output offset) of the k-th group a block's chain enters
+    uint32_t* blk_nent; uint32_t* blk_usize;// [blocks]
+    uint32_t* piece_base;                   // [blocks + 1]
+    DfPiece* pieces;                        // [cap_pieces]
+    uint32_t* bits;                         // one bit per output byte
+    DfState* st;
+    uint32_t cap_groups, cap_pieces;
+    uint64_t bits_bytes;
 };
 
 // Decode summary written by the finalise kernel

@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(ENC_WARPS * 32, ENC_CTAS_PER_SM)
 find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restrict__ scratch,
                  SubOut* __restrict__ subs, uint32_t* __restrict__ ticket, uint16_t* __restrict__ gtab)
 {
-    extern __shared__ __align__(16) uint16_t s_tab[];
+    B2_DYN_SHARED(uint16_t, s_tab);
     const uint32_t lane = lane_id();
     // ENC_SMEM_WARPS (6 of 8) warps keep their hash table in shared memory, the others in a global table that
     // lives in L1/L2: 32 warps per SM fit that way (192 KB of tables), and measured against 24 warps with every
@@ -504,9 +504,9 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
               EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket, uint8_t* __restrict__ idx_frag)
 {
     constexpr uint32_t NT = LAYOUT_THREADS;
-    __shared__ uint64_t part_bytes[NT];
-    __shared__ uint32_t part_chain[NT];
-    __shared__ EncodeResult s_res;
+    B2_SHARED_ARRAY(uint64_t, part_bytes, NT);
+    B2_SHARED_ARRAY(uint32_t, part_chain, NT);
+    B2_SHARED_VAR(EncodeResult, s_res);
     const uint32_t tid = threadIdx.x;
     const uint32_t nb = P.n_blocks;
     const uint32_t bc = P.block_checksum ? 4u : 0u;

@@ -5,7 +5,7 @@
 // by ONE small device->host copy of the result struct (no per-block host round trips).
 // Replaces the reference's LZ4F_cctx / LZ4F_dctx life cycle (lz4/lib/lz4frame.c:536-563, 1065-1090)
 // and the per-16 KB FFI call pattern of Conduit.hsc:308-314, 585-596 with batch calls.
-#include <cuda_runtime.h>
+#include "b2_cuda.h"
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -52,6 +52,7 @@ struct Small {                 // small device-side state, mirrored to pinned ho
     XxhState xxh;
     uint32_t ticket_dec, ticket_enc, crc_bad, hash_out;
     uint32_t walk[4];          // decoder-side block walk: chains published so far, done flag, walker ticket
+    DfState dfst;              // dataflow decode: tickets, first failure, byte counts
 };
 
 }  // namespace
@@ -65,6 +66,8 @@ struct b2lz4_ctx {
     Small* d_small = nullptr;
     Small* h_small = nullptr;                     // pinned
     DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stored, stage_in, stage_out, enc_tabs, ring, idx_frag, stage_in2, stage_out2;
+    DevBuf df_grp, df_heads, df_ent, df_nent, df_usize, df_pbase, df_pieces, df_bits;   // dataflow decode (decode_df.cu), allocated when a frame first needs them
+    uint32_t df_groups = 0, df_npieces = 0;       // their capacities
     size_t ring_pos = 0; uint32_t ring_hist = 0;     // streaming linked-block decode: next output offset / valid history bytes
     b2lz4_stats stats{};
     char cuda_err[256] = {0};
@@ -208,6 +211,8 @@ size_t b2lz4_create(b2lz4_ctx** out, int device, const b2lz4_prefs* prefs) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if ((e = cudaFuncSetAttribute(find_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)find_emit_smem_bytes())) != cudaSuccess) return fail(e, "cudaFuncSetAttribute");
+    if ((e = cudaFuncSetAttribute(df_links_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)df_links_smem_bytes())) != cudaSuccess) return fail(e, "cudaFuncSetAttribute");
     *out = ctx;
     return 0;
 }
@@ -219,7 +224,8 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->st) cudaStreamSynchronize(ctx->st);
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
-                       &ctx->chains, &ctx->outs, &ctx->stored, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2 }) b->release();
+                       &ctx->chains, &ctx->outs, &ctx->stored, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2,
+                       &ctx->df_grp, &ctx->df_heads, &ctx->df_ent, &ctx->df_nent, &ctx->df_usize, &ctx->df_pbase, &ctx->df_pieces, &ctx->df_bits }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
@@ -309,31 +315,31 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     if (sum) {                                   // serial XXH32 of the input on the second stream
         CU(cudaEventRecord(ctx->ev_in, ctx->st));
         CU(cudaStreamWaitEvent(ctx->st2, ctx->ev_in, 0));
-        if (flags & CL_SUM_RESET) { xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ds->xxh); ++launches; }
-        if (flags & CL_SUM_UPDATE) { xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>(d_src, n, nullptr, nullptr, &ds->xxh); ++launches; }
+        if (flags & CL_SUM_RESET) { B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st2, &ds->xxh); ++launches; }
+        if (flags & CL_SUM_UPDATE) { B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st2, d_src, n, nullptr, nullptr, &ds->xxh); ++launches; }
         CU(cudaEventRecord(ctx->ev_sum, ctx->st2));
     }
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
     if (P.n_subs) {
         uint32_t grid = std::min<uint32_t>((P.n_subs + ENC_WARPS - 1) / ENC_WARPS, (uint32_t)ctx->sm_count * (uint32_t)ENC_CTAS_PER_SM);
         CU(ctx->enc_tabs.ensure(find_emit_gtab_bytes(grid)));
-        find_emit_kernel<<<grid, ENC_WARPS * 32, find_emit_smem_bytes(), ctx->st>>>(
+        B2_LAUNCH(find_emit_kernel, grid, ENC_WARPS * 32, find_emit_smem_bytes(), ctx->st, 
             d_src, P, (uint8_t*)ctx->scratch.p, (SubOut*)ctx->subs.p, &ds->ticket_enc, (uint16_t*)ctx->enc_tabs.p);
         ++launches;
     }
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
-    layout_kernel<<<1, LAYOUT_THREADS, 0, ctx->st>>>(P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p,
+    B2_LAUNCH(layout_kernel, 1, LAYOUT_THREADS, 0, ctx->st, P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p,
                                            (BlockPlace*)ctx->bplaces.p, d_dst, cap, &ds->eres, &ds->ticket_enc,
                                            (flags & CL_INDEX_FRAGMENT) ? (uint8_t*)ctx->idx_frag.p : nullptr);
     ++launches;
     if (P.n_subs) {
         uint32_t grid = std::min<uint32_t>(P.n_subs, (uint32_t)ctx->sm_count * 8u);
-        gather_kernel<<<grid, 256, 0, ctx->st>>>(d_src, P, (const uint8_t*)ctx->scratch.p, (const SubOut*)ctx->subs.p,
+        B2_LAUNCH(gather_kernel, grid, 256, 0, ctx->st, d_src, P, (const uint8_t*)ctx->scratch.p, (const SubOut*)ctx->subs.p,
                                                  (const SubPlace*)ctx->places.p, (const BlockPlace*)ctx->bplaces.p,
                                                  d_dst, &ds->eres);
         ++launches;
         if (P.block_checksum) {
-            block_checksums_kernel<<<(P.n_blocks + 127) / 128, 128, 0, ctx->st>>>(P, (const BlockPlace*)ctx->bplaces.p,
+            B2_LAUNCH(block_checksums_kernel, (P.n_blocks + 127) / 128, 128, 0, ctx->st, P, (const BlockPlace*)ctx->bplaces.p,
                                                                                  d_dst, &ds->eres);
             ++launches;
         }
@@ -341,7 +347,7 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     if (sum) {
         CU(cudaStreamWaitEvent(ctx->st, ctx->ev_sum, 0));
         if (whole_frame) {
-            xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, d_dst, &ds->eres.content_checksum_off);
+            B2_LAUNCH(xxh32_digest_kernel, 1, 32, 0, ctx->st, &ds->xxh, &ds->hash_out, d_dst, &ds->eres.content_checksum_off);
             ++launches;
         }
     }
@@ -376,9 +382,31 @@ size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* 
 }
 
 // -------------------------------------------------------------------------------------- decompress
+// dataflow mode is on unless B2LZ4_DF=0 (then unindexed frames decode one warp per block, linked frames one warp per frame)
+static bool df_enabled() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_DF"); v = (e && *e == '0') ? 0 : 1; } return v == 1; }
+
 static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, uint8_t* d_dst, size_t cap,
                                 uint32_t mode, uint32_t cap_tables, uint32_t hist)
 {
+    DfWork W{};
+    if (mode & SCAN_DF) {
+        // workspaces of the dataflow path: whatever the context already owns (a frame that needs more says so through
+        // ERROR_allocation_failed + need_*, and the caller comes again); contexts made for foreign frames start with an estimate
+        if (ctx->df_groups) {
+            CU(ctx->df_grp.ensure(((size_t)cap_tables + 1) * sizeof(uint32_t)));
+            CU(ctx->df_nent.ensure((size_t)cap_tables * sizeof(uint32_t)));
+            CU(ctx->df_usize.ensure((size_t)cap_tables * sizeof(uint32_t)));
+            CU(ctx->df_pbase.ensure(((size_t)cap_tables + 1) * sizeof(uint32_t)));
+            CU(ctx->df_heads.ensure((size_t)ctx->df_groups * DF_G * sizeof(DfHead)));
+            CU(ctx->df_ent.ensure((size_t)ctx->df_groups * sizeof(uint2)));
+            CU(ctx->df_pieces.ensure((size_t)ctx->df_npieces * sizeof(DfPiece)));
+            CU(ctx->df_bits.ensure(cap / 8 + 64));
+        }
+        W.grp_base = (uint32_t*)ctx->df_grp.p; W.heads = (DfHead*)ctx->df_heads.p; W.ent = (uint2*)ctx->df_ent.p;
+        W.blk_nent = (uint32_t*)ctx->df_nent.p; W.blk_usize = (uint32_t*)ctx->df_usize.p; W.piece_base = (uint32_t*)ctx->df_pbase.p;
+        W.pieces = (DfPiece*)ctx->df_pieces.p; W.bits = (uint32_t*)ctx->df_bits.p; W.st = &ctx->d_small->dfst;
+        W.cap_groups = ctx->df_groups; W.cap_pieces = ctx->df_npieces; W.bits_bytes = ctx->df_bits.cap;
+    }
     CU(ctx->blocks.ensure((size_t)cap_tables * sizeof(BlockRef)));
     CU(ctx->pieces.ensure((size_t)cap_tables * sizeof(Piece)));
     CU(ctx->chains.ensure((size_t)cap_tables * sizeof(Chain)));
@@ -388,25 +416,35 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
     uint32_t launches = 0;
     CU(cudaMemsetAsync(&ds->crc_bad, 0xFF, sizeof(uint32_t), ctx->st));
     CU(cudaEventRecord(ctx->ev[0], ctx->st));
-    frame_scan_kernel<<<1, 256, 0, ctx->st>>>(d_src, n, cap, mode, &ds->fi, (BlockRef*)ctx->blocks.p, cap_tables,
-                                              (Piece*)ctx->pieces.p, cap_tables, (Chain*)ctx->chains.p, (uint32_t*)ctx->stored.p, ds->walk);
+    B2_LAUNCH(frame_scan_kernel, 1, 256, 0, ctx->st, d_src, n, cap, mode, &ds->fi, (BlockRef*)ctx->blocks.p, cap_tables,
+                                              (Piece*)ctx->pieces.p, cap_tables, (Chain*)ctx->chains.p, (uint32_t*)ctx->stored.p, ds->walk, W);
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
-    decode_chains_kernel<<<ctx->sm_count * (64 / DEC_WARPS), DEC_WARPS * 32, 0, ctx->st>>>(
+    B2_LAUNCH(decode_chains_kernel, ctx->sm_count * (64 / DEC_WARPS), DEC_WARPS * 32, 0, ctx->st, 
         d_src, n, d_dst, cap, mode, &ds->fi, (BlockRef*)ctx->blocks.p, (Piece*)ctx->pieces.p, (Chain*)ctx->chains.p, cap_tables,
         (uint32_t*)ctx->stored.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec, ds->walk, hist);
-    copy_stored_kernel<<<ctx->sm_count * 8, 256, 0, ctx->st>>>(d_src, d_dst, cap, &ds->fi, (const Piece*)ctx->pieces.p,
+    B2_LAUNCH(copy_stored_kernel, ctx->sm_count * 8, 256, 0, ctx->st, d_src, d_dst, cap, &ds->fi, (const Piece*)ctx->pieces.p,
                                                              (const Chain*)ctx->chains.p, (const uint32_t*)ctx->stored.p);
-    verify_block_checksums_kernel<<<std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st>>>(
+    if (mode & SCAN_DF) {                         // every one of these returns at once unless the scan chose the dataflow path
+        const BlockRef* bl = (const BlockRef*)ctx->blocks.p;
+        B2_LAUNCH(df_links_kernel, ctx->sm_count * 3, DF_WARPS * 32, df_links_smem_bytes(), ctx->st, d_src, n, &ds->fi, bl, W);
+        B2_LAUNCH(df_stitch_kernel, std::max(1u, std::min((cap_tables + 127u) / 128u, 1024u)), 128, 0, ctx->st, d_src, &ds->fi, bl, W);
+        B2_LAUNCH(df_layout_kernel, 1, 256, 0, ctx->st, &ds->fi, (BlockRef*)ctx->blocks.p, cap, W);
+        B2_LAUNCH(df_pieces_kernel, ctx->sm_count * 4, 256, 0, ctx->st, &ds->fi, bl, W);
+        B2_LAUNCH(decode_df_kernel, ctx->sm_count * B2_DF_MINCTAS, DEC_WARPS * 32, 0, ctx->st, d_src, n, d_dst, cap, &ds->fi, bl, W, hist);
+        launches += 5;
+    }
+    B2_LAUNCH(verify_block_checksums_kernel, std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st, 
         d_src, &ds->fi, (const BlockRef*)ctx->blocks.p, &ds->crc_bad);
     CU(cudaEventRecord(ctx->ev[2], ctx->st));
-    decode_finalize_kernel<<<1, 256, 0, ctx->st>>>(&ds->fi, (const Piece*)ctx->pieces.p, (const PieceOut*)ctx->outs.p,
+    B2_LAUNCH(decode_finalize_kernel, 1, 256, 0, ctx->st, &ds->fi, (const Piece*)ctx->pieces.p, (const PieceOut*)ctx->outs.p,
                                                    &ds->crc_bad, &ds->dres, &ds->ticket_dec);
+    if (mode & SCAN_DF) { B2_LAUNCH(df_finalize_kernel, 1, 32, 0, ctx->st, &ds->fi, &ds->crc_bad, &ds->dres, W); ++launches; }
     // content checksum over the output (lz4frame.c:1676-1677, 1734-1745); the kernels return at once
     // when the frame carries none
     if (!(mode & SCAN_BATCH)) {                   // a batch of a streamed frame keeps its running checksum (caller updates it)
-        xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
-        xxh32_stream_kernel<<<1, 256, 0, ctx->st>>>(d_dst, 0, &ds->dres.total_out, &ds->fi.desc.content_checksum, &ds->xxh);
-        content_check_kernel<<<1, 32, 0, ctx->st>>>(&ds->fi, &ds->xxh, &ds->dres);
+        B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ds->xxh);
+        B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st, d_dst, 0, &ds->dres.total_out, &ds->fi.desc.content_checksum, &ds->xxh);
+        B2_LAUNCH(content_check_kernel, 1, 32, 0, ctx->st, &ds->fi, &ds->xxh, &ds->dres);
         launches += 3;
     }
     launches += 5;
@@ -424,10 +462,20 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
 static uint32_t tables_for(size_t n, size_t cap) {
     return (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, std::max<uint64_t>(4096, (n >> 12) + (cap >> 16) + 64));
 }
+// a context that decodes foreign frames (no index expected) sizes the dataflow workspaces up front; others wait for a
+// frame that asks for them
+static void df_presize(b2lz4_ctx* ctx, size_t n, size_t cap) {
+    if (!df_enabled()) return;
+    if (ctx->prefs.use_index && !ctx->df_groups) return;
+    const uint64_t g = n / DF_G + tables_for(n, cap) + 16, p = g + cap / DF_STORED_PIECE + 16;
+    if (g > ctx->df_groups) ctx->df_groups = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, g + g / 8);
+    if (p > ctx->df_npieces) ctx->df_npieces = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, p + p / 8);
+}
 // queues the first decode attempt on ctx->st without waiting; decompress_device_impl(..., launched0 = true) completes it
 static size_t decompress_begin(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, uint32_t hist, uint32_t mode0) {
     ctx->stats = b2lz4_stats{};
-    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK;
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK | (df_enabled() ? SCAN_DF : 0u);
+    df_presize(ctx, n, cap);
     return decompress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, mode, tables_for(n, cap), hist);
 }
 size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed) {
@@ -443,8 +491,9 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
     static uint8_t* dummy = nullptr;
     uint8_t* dst = (uint8_t*)d_dst;
     if (!dst) { if (!dummy) CU(cudaMalloc(&dummy, 256)); dst = dummy; }
-    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK;
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK | (df_enabled() ? SCAN_DF : 0u);
     uint32_t cap_tables = tables_for(n, cap);
+    if (!launched0) df_presize(ctx, n, cap);
     for (int attempt = 0; attempt < 4; ++attempt) {
         if (!(launched0 && attempt == 0)) {
             r = decompress_launch(ctx, (const uint8_t*)d_src, n, dst, cap, mode, cap_tables, hist);
@@ -454,7 +503,11 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
         const FrameIndex& fi = ctx->h_small->fi;
         const DecodeResult& dr = ctx->h_small->dres;
         if (fi.err == E_allocation_failed && attempt < 3) {            // tables too small: grow and rerun
-            cap_tables = std::max(fi.need_blocks, fi.need_pieces) + 16;
+            if (fi.df) {
+                cap_tables = std::max(cap_tables, fi.need_blocks + 16);
+                ctx->df_groups = std::max(ctx->df_groups, fi.need_groups + 16);
+                ctx->df_npieces = std::max(ctx->df_npieces, fi.need_pieces + 16);
+            } else cap_tables = std::max(fi.need_blocks, fi.need_pieces) + 16;
             ++ctx->stats.retries; continue;
         }
         if (fi.indexed && (mode & SCAN_USE_INDEX) && dr.err != OK && attempt < 3) {
@@ -534,7 +587,7 @@ struct SumChain {
         if (ctx->sum_host) {
             XxhState z{}; z.v[0] = XP1 + XP2; z.v[1] = XP2; z.v[2] = 0; z.v[3] = 0u - XP1;    // xxhash.c:437-449
             *ctx->h_xxh = z;
-        } else { cudaSetDevice(ctx->device); xxh32_reset_kernel<<<1, 32, 0, ctx->st2>>>(&ctx->d_small->xxh); ++launches; }
+        } else { cudaSetDevice(ctx->device); B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st2, &ctx->d_small->xxh); ++launches; }
     }
     // hashes p[0, len) (device memory of lane `ln`) after `after` (an event on the lane's stream, or null); records ln->ev_sum
     cudaError_t update(b2lz4_ctx* ln, const uint8_t* p, size_t len, cudaEvent_t after) {
@@ -543,12 +596,12 @@ struct SumChain {
             if ((e = cudaSetDevice(ln->device)) != cudaSuccess) return e;
             if (after && (e = cudaStreamWaitEvent(ln->st2, after, 0)) != cudaSuccess) return e;
             if (prev && (e = cudaStreamWaitEvent(ln->st2, prev, 0)) != cudaSuccess) return e;
-            xxh32_stream_kernel<<<1, 256, 0, ln->st2>>>(p, len, nullptr, nullptr, ctx->h_xxh);
+            B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ln->st2, p, len, nullptr, nullptr, ctx->h_xxh);
             if ((e = cudaEventRecord(ln->ev_sum, ln->st2)) != cudaSuccess) return e;
             prev = ln->ev_sum;
         } else {
             if (after && (e = cudaStreamWaitEvent(ctx->st2, after, 0)) != cudaSuccess) return e;
-            xxh32_stream_kernel<<<1, 256, 0, ctx->st2>>>(p, len, nullptr, nullptr, &ctx->d_small->xxh);
+            B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st2, p, len, nullptr, nullptr, &ctx->d_small->xxh);
             if ((e = cudaEventRecord(ln->ev_sum, ctx->st2)) != cudaSuccess) return e;
         }
         ++launches;
@@ -925,7 +978,7 @@ size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, voi
             if (multi_dev(ctx)) { r = ensure_lanes(ctx, 1); if (r) return r; SumChain sc{ctx}; sc.reset(); }
             else {
                 ctx->sum_host = false;
-                xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ctx->d_small->xxh);
+                B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ctx->d_small->xxh);
                 CU(cudaStreamSynchronize(ctx->st));
             }
         }
@@ -948,7 +1001,7 @@ size_t b2lz4_content_checksum(b2lz4_ctx* ctx, uint32_t* out) {
     }
     Small* ds = ctx->d_small;
     CU(cudaStreamSynchronize(ctx->st2));
-    xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, nullptr, nullptr);
+    B2_LAUNCH(xxh32_digest_kernel, 1, 32, 0, ctx->st, &ds->xxh, &ds->hash_out, nullptr, nullptr);
     CU(cudaMemcpyAsync(&ctx->h_small->hash_out, &ds->hash_out, 4, cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
     CU(cudaGetLastError());
@@ -998,7 +1051,7 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     Small* ds = ctx->d_small;
     if (flags & B2LZ4_STREAM_FIRST) {
         ctx->ring_pos = 65536; ctx->ring_hist = 0; ctx->sum_host = false;
-        if (info->content_checksum) xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
+        if (info->content_checksum) B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ds->xxh);
     }
     if (n == 0) { CU(cudaStreamSynchronize(ctx->st)); return 0; }
     if (!legacy && info->block_independent) {
@@ -1052,7 +1105,7 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     ctx->prefs.use_index = keep_index;
     if (b2lz4_is_error(r)) return r;
     if (consumed != hs + n + 4) return err_code(E_decompressionFailed);   // an EndMark inside the batch: not whole blocks
-    if (info->content_checksum && r) xxh32_stream_kernel<<<1, 256, 0, ctx->st>>>(dout, r, nullptr, nullptr, &ds->xxh);
+    if (info->content_checksum && r) B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st, dout, r, nullptr, nullptr, &ds->xxh);
     if (r) CU(cudaMemcpyAsync(dst, dout, r, cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
     CU(cudaGetLastError());
@@ -1068,9 +1121,9 @@ size_t b2lz4_xxh32_device(b2lz4_ctx* ctx, const void* d_src, size_t n, uint32_t*
     if (!ctx || !out || (!d_src && n)) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
     Small* ds = ctx->d_small;
-    xxh32_reset_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh);
-    xxh32_stream_kernel<<<1, 256, 0, ctx->st>>>((const uint8_t*)d_src, n, nullptr, nullptr, &ds->xxh);
-    xxh32_digest_kernel<<<1, 32, 0, ctx->st>>>(&ds->xxh, &ds->hash_out, nullptr, nullptr);
+    B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ds->xxh);
+    B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st, (const uint8_t*)d_src, n, nullptr, nullptr, &ds->xxh);
+    B2_LAUNCH(xxh32_digest_kernel, 1, 32, 0, ctx->st, &ds->xxh, &ds->hash_out, nullptr, nullptr);
     CU(cudaMemcpyAsync(&ctx->h_small->hash_out, &ds->hash_out, 4, cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
     CU(cudaGetLastError());

@@ -1,6 +1,6 @@
 // kernels.h — launch-side declarations of the sm_100a kernels (decode.cu, encode.cu, xxh32.cu).
 #pragma once
-#include <cuda_runtime.h>
+#include "b2_cuda.h"
 #include <stdint.h>
 #include "device_types.h"
 
@@ -31,7 +31,15 @@ constexpr int ENC_HLOG  = B2_ENC_HLOG;  // 4096-entry u16 hash table per warp (8
 #endif
 constexpr uint32_t ENC_UNIT = 1u << B2_ENC_UNIT_LOG2;   // bytes one match-finder warp parses at a time (a domain = sub-block holds several)
 constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
+#ifndef B2_DF_WARPS
+#define B2_DF_WARPS 8
+#endif
+constexpr int DF_WARPS = B2_DF_WARPS;            // warps per CTA in df_links_kernel (9.3 KB of shared memory each)
+#ifndef B2_DF_MINCTAS
+#define B2_DF_MINCTAS 4
+#endif
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
+                  SCAN_DF = 32u,              // frames without a usable index go to the dataflow kernels (decode_df.cu)
                   SCAN_LEGACY = 8u,
                   SCAN_OVERLAP_WALK = 16u };  // plain independent-block frames: walk the block headers inside the decoder kernel   // blocks of a legacy frame (lz4_Frame_format.md:338-386): 8 MB, always compressed, no flag bit
 constexpr uint32_t LEGACY_BLOCK = 8u << 20;
@@ -39,7 +47,7 @@ constexpr uint32_t LEGACY_BLOCK = 8u << 20;
 // ---- decode
 __global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_cap, uint32_t mode,
                                   FrameIndex* fi, BlockRef* blocks, uint32_t cap_blocks,
-                                  Piece* pieces, uint32_t cap_pieces, Chain* chains, uint32_t* stored_list, uint32_t* walk);
+                                  Piece* pieces, uint32_t cap_pieces, Chain* chains, uint32_t* stored_list, uint32_t* walk, DfWork W);
 __global__ void copy_stored_kernel(const uint8_t* src, uint8_t* dst, uint64_t dst_cap, const FrameIndex* fi,
                                    const Piece* pieces, const Chain* chains, const uint32_t* stored_list);
 __global__ void decode_chains_kernel(const uint8_t* src, uint64_t n_src, uint8_t* dst, uint64_t dst_cap, uint32_t mode,
@@ -49,6 +57,16 @@ __global__ void decode_finalize_kernel(const FrameIndex* fi, const Piece* pieces
                                        const uint32_t* block_crc_bad, DecodeResult* res, uint32_t* ticket);
 __global__ void verify_block_checksums_kernel(const uint8_t* src, const FrameIndex* fi,
                                               const BlockRef* blocks, uint32_t* first_bad);
+
+// ---- decode, dataflow path
+__global__ void df_links_kernel(const uint8_t* src, uint64_t n_src, const FrameIndex* fi, const BlockRef* blocks, DfWork W);
+size_t df_links_smem_bytes();
+__global__ void df_stitch_kernel(const uint8_t* src, const FrameIndex* fi, const BlockRef* blocks, DfWork W);
+__global__ void df_layout_kernel(FrameIndex* fi, BlockRef* blocks, uint64_t dst_cap, DfWork W);
+__global__ void df_pieces_kernel(const FrameIndex* fi, const BlockRef* blocks, DfWork W);
+__global__ void decode_df_kernel(const uint8_t* src, uint64_t n_src, uint8_t* dst, uint64_t dst_cap,
+                                 const FrameIndex* fi, const BlockRef* blocks, DfWork W, uint32_t hist);
+__global__ void df_finalize_kernel(const FrameIndex* fi, const uint32_t* block_crc_bad, DecodeResult* res, DfWork W);
 
 // ---- encode
 __global__ void find_emit_kernel(const uint8_t* src, EncParams P, uint8_t* scratch, SubOut* subs, uint32_t* ticket, uint16_t* gtab);

@@ -6,7 +6,7 @@
 // that collects whole blocks in pinned staging buffers and hands them to the GPU a batch at a time
 // (b2lz4_compress_blocks_host / b2lz4_decompress_blocks_host).  Nothing in this file compresses or
 // decompresses: without a CUDA device the calls return ERROR_cudaFailure.
-#include <cuda_runtime.h>
+#include "b2_cuda.h"
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>

@@ -31,10 +31,10 @@ xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t
 {
     if (enable_ptr && !*enable_ptr) return;      // e.g. &FrameIndex::desc.content_checksum
     if (n_ptr) n = *n_ptr;                        // e.g. &DecodeResult::total_out
-    __shared__ __align__(16) uint8_t tile[2][XXH_TILE];
-    __shared__ XxhState s;
-    __shared__ uint64_t s_pos;          // first byte of the full-stripe region
-    __shared__ uint64_t s_stripes;      // number of 16-byte stripes in it
+    B2_SHARED_ARRAY(uint8_t, tile, 2 * XXH_TILE);
+    B2_SHARED_VAR(XxhState, s);
+    B2_SHARED_VAR(uint64_t, s_pos);          // first byte of the full-stripe region
+    B2_SHARED_VAR(uint64_t, s_stripes);      // number of 16-byte stripes in it
     const uint32_t tid = threadIdx.x;
     if (tid == 0) {
         s = *st;
@@ -63,7 +63,7 @@ xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t
     uint32_t acc = s.v[tid & 3u];
     if (ntiles) {
         uint64_t len0 = stripes * 16 < XXH_TILE ? stripes * 16 : XXH_TILE;
-        group_copy(tile[0], data + pos, len0, tid, 256);
+        group_copy(tile, data + pos, len0, tid, 256);
     }
     __syncthreads();
     for (uint64_t t = 0; t < ntiles; ++t) {
@@ -72,17 +72,17 @@ xxh32_stream_kernel(const uint8_t* __restrict__ data, uint64_t n, const uint64_t
         if (t + 1 < ntiles) {                                                 // prefetch the next tile
             const uint64_t off2 = off + XXH_TILE;
             const uint64_t len2 = (stripes * 16 - off2) < XXH_TILE ? (stripes * 16 - off2) : XXH_TILE;
-            if (tid >= 32) group_copy(tile[(t + 1) & 1], data + pos + off2, len2, tid - 32, 224);
+            if (tid >= 32) group_copy(tile + ((t + 1) & 1) * XXH_TILE, data + pos + off2, len2, tid - 32, 224);
         }
         if (tid < 4u) {
-            const uint32_t* w = (const uint32_t*)tile[t & 1] + tid;
+            const uint32_t* w = (const uint32_t*)(tile + (t & 1) * XXH_TILE) + tid;
             const uint32_t ns = (uint32_t)(len >> 4);
             uint32_t i = 0;
             for (; i + 8 <= ns; i += 8) {
                 uint32_t x[8];
                 #pragma unroll
                 for (int k = 0; k < 8; ++k) x[k] = w[4u * (i + k)];
-#if B2_XXH_CHAIN == 0
+#if B2_XXH_CHAIN == 0 || !B2_PTX
                 #pragma unroll
                 for (int k = 0; k < 8; ++k) acc = xxh32_round(acc, x[k]);
 #else
