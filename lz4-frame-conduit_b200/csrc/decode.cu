@@ -42,7 +42,7 @@ __device__ B2_NOINLINE void walk_blocks_df(const uint8_t* __restrict__ src, uint
     const uint32_t bc = s.desc.block_checksum ? 4u : 0u;
     const uint32_t cc = s.desc.content_checksum ? 4u : 0u;
     uint64_t ip = s.desc.header_size;
-    uint32_t nb = 0, groups = 0, stored_pieces = 0;
+    uint32_t nb = 0, groups = 0, tickets = 0;
     Err err = OK;
     for (;;) {
         if (n - ip < 4) { err = E_noEndMark; break; }
@@ -59,8 +59,8 @@ __device__ B2_NOINLINE void walk_blocks_df(const uint8_t* __restrict__ src, uint
             blocks[nb] = br;
             W.grp_base[nb] = groups;
         }
-        if (stored) stored_pieces += (cs + DF_STORED_PIECE - 1u) / DF_STORED_PIECE;
-        else groups += (cs + DF_G - 1u) / DF_G;
+        if (stored) tickets += 1u;
+        else { groups += (cs + DF_G - 1u) / DF_G; tickets += cs / (3u * DF_BATCH) + 2u; }   // a sequence takes at least 3 bytes
         ++nb;
         ip += (uint64_t)cs + bc;
     }
@@ -68,16 +68,16 @@ __device__ B2_NOINLINE void walk_blocks_df(const uint8_t* __restrict__ src, uint
         if (n - ip < 4) err = E_noEndMark;
         else { s.stored_content_checksum = ld_le32_dev(src + ip); ip += 4; }
     }
-    s.need_blocks = nb; s.need_groups = groups; s.need_pieces = groups + stored_pieces;
-    if (err == OK && (nb > cap_blocks || !W.cap_groups || groups > W.cap_groups || s.need_pieces > W.cap_pieces)) err = E_allocation_failed;
+    s.need_blocks = nb; s.need_groups = groups; s.need_tickets = tickets; s.need_pieces = 0;
+    if (err == OK && (nb > cap_blocks || !W.cap_groups || groups > W.cap_groups || tickets > W.cap_tickets)) err = E_allocation_failed;
     if (err == OK) W.grp_base[nb] = groups;
     s.err = err;
     s.n_blocks = nb; s.n_pieces = 0; s.n_chains = 0; s.n_stored = 0;
     s.consumed = ip; s.consumed_with_index = ip;
     s.total_out = (uint64_t)nb * s.block_size;                   // upper bound until df_layout_kernel knows
     s.layout_known = 0; s.walk_pending = 0; s.df = 1;
-    DfState st; st.bad_key = 0xFFFFFFFFFFFFFFFFull; st.produced = 0; st.total_out = 0; st.n_pieces = 0;
-    st.ticket_links = 0; st.ticket_decode = 0; st.pad = 0;
+    DfState st; st.bad_key = 0xFFFFFFFFFFFFFFFFull; st.produced = 0; st.total_out = 0; st.n_tickets = 0; st.n_units = 0;
+    st.ticket_links = 0; st.ticket_units = 0; st.ticket_tk = 0; st.pad = 0;
     *W.st = st;
 }
 

@@ -25,97 +25,73 @@ struct Cursor {            // what the warp knows about the piece it is decoding
     bool p_done;           // ... and whether the piece ended with it
     uint32_t reach;        // a match at output position m may reach back `m + reach` bytes (mod 2^32):
                            // independent piece: -piece_start;  linked: bytes of earlier output in front of the block
-    // dataflow mode (decode_df.cu): bytes below piece_lo are written by OTHER warps; bit i of `bits` = output byte i of
-    // the destination buffer is final.  abs0 = offset of the owning block's first output byte in that buffer.
-    uint32_t* bits;
+    // dataflow mode (decode_df.cu): this piece is one ticket of a unit that a whole CTA decodes; bytes in front of it are
+    // written by OTHER warps of the CTA.  abs0 = offset of the owning block's first output byte in the destination buffer.
+    DfShared df;
     int64_t abs0;
-    uint32_t piece_lo;
+    bool solo;             // the piece runs alone (every earlier byte is final, nobody reads the map): no waits, no marks
 };
 
-// ---- dataflow helpers: the "final bytes" bitmap.  A writer stores its bytes, fences, then sets their bits; a reader
-// loads the bits with acquire semantics and only then the bytes (past L1, which is not coherent between SMs).
-__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
-#if B2_PTX
-    uint32_t v; asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
-#else
-    return __atomic_load_n(p, __ATOMIC_ACQUIRE);
-#endif
-}
-// all of the bytes [a, b) final?  Positions below 0 are history in front of the buffer: final by construction.
-__device__ __forceinline__ bool bits_ready(const uint32_t* bits, int64_t a, int64_t b) {
-    if (a < 0) a = 0;
-    if (b <= a) return true;
-    const uint64_t w0 = (uint64_t)a >> 5, w1 = (uint64_t)(b - 1) >> 5;
+// ---- dataflow helpers.  The CTA keeps, in shared memory, one bit per output byte for a sliding window of the unit's
+// output (circular, DF_WIN_BYTES long) and a watermark below which every byte is final.  A writer stores its bytes,
+// fences (CTA scope: writer and readers sit on one SM and share its L1), then sets their bits; a reader that finds the
+// bits set fences and then loads the bytes.  Positions are absolute offsets in the destination buffer; negative ones are
+// history in front of it (earlier batches of a linked frame): final by construction.
+__device__ __forceinline__ bool df_ready(const DfShared& S, int64_t a, int64_t b) {
+    const int64_t F = (int64_t)*S.final_below;
+    if (b <= F) return true;
+    if (a < F) a = F;
+    const uint32_t w0 = (uint32_t)((uint64_t)a >> 5), w1 = (uint32_t)((uint64_t)(b - 1) >> 5);
     const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
-    if (w0 == w1) { const uint32_t m = m0 & m1; return (ld_acquire(bits + w0) & m) == m; }
-    if ((ld_acquire(bits + w0) & m0) != m0) return false;
-    for (uint64_t w = w0 + 1; w < w1; ++w) if (ld_acquire(bits + w) != 0xFFFFFFFFu) return false;
-    return (ld_acquire(bits + w1) & m1) == m1;
+    const volatile uint32_t* bits = S.bits;
+    if (w0 == w1) { const uint32_t m = m0 & m1; return (bits[w0 & DF_WIN_MASK] & m) == m; }
+    if ((bits[w0 & DF_WIN_MASK] & m0) != m0) return false;
+    for (uint32_t w = w0 + 1; w != w1; ++w) if (bits[w & DF_WIN_MASK] != 0xFFFFFFFFu) return false;
+    return (bits[w1 & DF_WIN_MASK] & m1) == m1;
 }
 // the same question asked by the whole warp about a long range (uniform answer)
-__device__ __forceinline__ bool bits_ready_warp(const uint32_t* bits, int64_t a, int64_t b, uint32_t lane) {
-    if (a < 0) a = 0;
-    if (b <= a) return true;
-    const uint64_t w0 = (uint64_t)a >> 5, w1 = (uint64_t)(b - 1) >> 5;
+__device__ __forceinline__ bool df_ready_warp(const DfShared& S, int64_t a, int64_t b, uint32_t lane) {
+    int64_t F = 0;
+    if (lane == 0) F = (int64_t)*S.final_below;
+    F = __shfl_sync(FULL_MASK, F, 0);
+    if (b <= F) return true;
+    if (a < F) a = F;
+    const uint32_t w0 = (uint32_t)((uint64_t)a >> 5), w1 = (uint32_t)((uint64_t)(b - 1) >> 5);
     const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
+    const volatile uint32_t* bits = S.bits;
     bool ok = true;
-    for (uint64_t w = w0 + lane; w <= w1 && ok; w += 32) {
+    for (uint32_t k = lane; k <= w1 - w0 && ok; k += 32u) {
+        const uint32_t w = w0 + k;
         uint32_t m = 0xFFFFFFFFu;
         if (w == w0) m &= m0;
         if (w == w1) m &= m1;
-        ok = (ld_acquire(bits + w) & m) == m;
+        ok = (bits[w & DF_WIN_MASK] & m) == m;
     }
     return __all_sync(FULL_MASK, ok);
 }
 // marks [a, b) final; the caller has fenced its stores.  One lane, short ranges (a few words).
-__device__ __forceinline__ void bits_mark(uint32_t* bits, uint64_t a, uint64_t b) {
+__device__ __forceinline__ void df_mark(const DfShared& S, uint64_t a, uint64_t b) {
     if (b <= a) return;
-    const uint64_t w0 = a >> 5, w1 = (b - 1) >> 5;
+    const uint32_t w0 = (uint32_t)(a >> 5), w1 = (uint32_t)((b - 1) >> 5);
     const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
-    if (w0 == w1) { atomicOr(bits + w0, m0 & m1); return; }
-    atomicOr(bits + w0, m0);
-    for (uint64_t w = w0 + 1; w < w1; ++w) atomicOr(bits + w, 0xFFFFFFFFu);
-    atomicOr(bits + w1, m1);
+    if (w0 == w1) { atomicOr(S.bits + (w0 & DF_WIN_MASK), m0 & m1); return; }
+    atomicOr(S.bits + (w0 & DF_WIN_MASK), m0);
+    for (uint32_t w = w0 + 1; w != w1; ++w) atomicOr(S.bits + (w & DF_WIN_MASK), 0xFFFFFFFFu);
+    atomicOr(S.bits + (w1 & DF_WIN_MASK), m1);
 }
-// ... by the whole warp, any length (every lane has fenced its stores and the warp has synchronised)
-__device__ __forceinline__ void bits_mark_warp(uint32_t* bits, uint64_t a, uint64_t b, uint32_t lane) {
+// ... by the whole warp, any length below the window (every lane has fenced its stores and the warp has synchronised);
+// `set` = false clears the bits again (retiring a ticket)
+__device__ __forceinline__ void df_mark_warp(const DfShared& S, uint64_t a, uint64_t b, uint32_t lane, bool set = true) {
     if (b <= a) return;
-    const uint64_t w0 = a >> 5, w1 = (b - 1) >> 5;
+    const uint32_t w0 = (uint32_t)(a >> 5), w1 = (uint32_t)((b - 1) >> 5);
     const uint32_t m0 = 0xFFFFFFFFu << ((uint32_t)a & 31u), m1 = 0xFFFFFFFFu >> (31u - ((uint32_t)(b - 1) & 31u));
-    for (uint64_t w = w0 + lane; w <= w1; w += 32) {
+    for (uint32_t k = lane; k <= w1 - w0; k += 32u) {
+        const uint32_t w = w0 + k;
         uint32_t m = 0xFFFFFFFFu;
         if (w == w0) m &= m0;
         if (w == w1) m &= m1;
-        atomicOr(bits + w, m);
+        if (set) atomicOr(S.bits + (w & DF_WIN_MASK), m); else atomicAnd(S.bits + (w & DF_WIN_MASK), ~m);
     }
-}
-// copies whose source was written by another SM read it past L1
-__device__ __forceinline__ void lane_copy_cg(uint8_t* d, const uint8_t* s, uint32_t n) {
-    uint32_t k = 0;
-    for (; k + 4 <= n; k += 4) {
-        uint8_t a = __ldcg(s + k), b = __ldcg(s + k + 1), c = __ldcg(s + k + 2), e = __ldcg(s + k + 3);
-        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
-    }
-    for (; k < n; ++k) d[k] = __ldcg(s + k);
-}
-__device__ __forceinline__ void lane_match_cg(uint8_t* d, uint32_t off, uint32_t n) {
-    const uint8_t* s = d - off;
-    uint32_t r = 0;
-    for (uint32_t k = 0; k < n; ++k) { d[k] = __ldcg(s + r); r = (r + 1 == off) ? 0u : r + 1; }
-}
-__device__ __forceinline__ void group_copy_cg(uint8_t* dst, const uint8_t* src, uint64_t n, uint32_t tid, uint32_t nthreads) {
-    uint32_t head = (uint32_t)((4u - ((uintptr_t)dst & 3u)) & 3u);
-    if (head > n) head = (uint32_t)n;
-    if (tid < head) dst[tid] = __ldcg(src + tid);
-    dst += head; src += head; n -= head;
-    const uint64_t nw = n >> 2;
-    const uint32_t sh = (uint32_t)((uintptr_t)src & 3u) * 8u;
-    const uint32_t* sw = (const uint32_t*)((uintptr_t)src & ~(uintptr_t)3);
-    uint32_t* dw = (uint32_t*)dst;
-    if (sh == 0) { for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = __ldcg(sw + i); }
-    else { for (uint64_t i = tid; i < nw; i += nthreads) dw[i] = __funnelshift_r(__ldcg(sw + i), __ldcg(sw + i + 1), sh); }
-    const uint64_t done = nw << 2;
-    if (tid < (uint32_t)(n - done)) dst[done + tid] = __ldcg(src + done + tid);
 }
 
 // Per-lane byte copy of n bytes; loads are batched four at a time ahead of the stores so that a lane
@@ -232,9 +208,8 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
     uint32_t i_fast = DF ? (iend >= 288u ? (pend < iend - 287u ? pend : iend - 287u) : 0u) : (pend >= 288u ? pend - 287u : 0u);
     const uint32_t olim = oend < opend ? oend : opend;
     uint32_t o_fast = DF ? (oend >= 560u ? (opend < oend - 559u ? opend : oend - 559u) : 0u) : (olim >= 560u ? olim - 559u : 0u);
-    const uint32_t piece_lo = DF ? c.piece_lo : 0u;
-    uint32_t* const bits = DF ? c.bits : nullptr;
     const int64_t abs0 = DF ? c.abs0 : 0;
+    const bool solo = DF ? c.solo : true;
     asm volatile("" : "+r"(i_fast), "+r"(o_fast));                          // keep them in registers (no re-derivation per sequence)
     uint32_t err = 0;
     if (pend == ip) return E_decompressionFailed;                           // empty input (lz4.c:1702)
@@ -433,21 +408,21 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 const uint32_t len = __shfl_sync(FULL_MASK, my_ll, j);
                 group_copy_small(dp + o, sp + l, len, lane, 32);
             }
-            if (DF) {                                                       // literals never wait: publish them at once
-                __threadfence();
+            if (DF && !solo) {                                              // literals never wait: publish them at once
+                __threadfence_block();
                 __syncwarp();
-                if (act && my_ll <= LANE_CAP) bits_mark(bits, (uint64_t)(abs0 + my_op), (uint64_t)(abs0 + my_op) + my_ll);
+                if (act && my_ll <= LANE_CAP) df_mark(c.df, (uint64_t)(abs0 + my_op), (uint64_t)(abs0 + my_op) + my_ll);
                 longm = longm0;
                 while (longm) {
                     const int j = __ffs(longm) - 1; longm &= longm - 1;
                     const uint32_t o = __shfl_sync(FULL_MASK, my_op, j), len = __shfl_sync(FULL_MASK, my_ll, j);
-                    bits_mark_warp(bits, (uint64_t)(abs0 + o), (uint64_t)(abs0 + o) + len, lane);
+                    df_mark_warp(c.df, (uint64_t)(abs0 + o), (uint64_t)(abs0 + o) + len, lane);
                 }
             }
         }
         __syncwarp();
         // ---- matches, in rounds
-        if (!DF) {
+        if (!DF || solo) {
             const uint32_t my_mop = my_op + my_ll;
             // end of the bytes read, relative to the match destination: -(off) + min(ml, off)  (<= 0)
             const int32_t my_need = (int32_t)(my_ml < my_off ? my_ml : my_off) - (int32_t)my_off;
@@ -473,64 +448,53 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 __syncwarp();
             }
         } else {
-            // dataflow: a match whose source starts below piece_lo reads bytes other warps write; it goes when their bits
-            // are set.  Inside the piece the watermark rule above still applies (and costs no memory traffic).
+            // dataflow: every byte of the unit's output has a "final" bit (literals were marked above, matches are marked as
+            // they are copied, by whichever warp of the CTA copies them).  A match goes as soon as the bits of the bytes IT reads
+            // are set — it waits for nothing else, and nothing waits for it but the matches that really read it.
             const uint32_t my_mop = my_op + my_ll;
             const uint32_t my_span = my_ml < my_off ? my_ml : my_off;       // bytes of the source window that are read
-            const int32_t my_need = (int32_t)my_span - (int32_t)my_off;
-            const bool my_ext = my_off > my_mop - piece_lo;                  // the source starts below piece_lo (also true for history / earlier blocks)
-            // external part of my source, in buffer coordinates: [xa, xb)
-            const int64_t xa = abs0 + (int64_t)my_mop - (int64_t)my_off;
-            const int64_t xe = xa + my_span, xl = abs0 + piece_lo;
-            const int64_t xb = xe < xl ? xe : xl;
-            bool ext_ok = !my_ext;
+            const int64_t xa = abs0 + (int64_t)my_mop - (int64_t)my_off, xb = xa + my_span;
             uint32_t pending = __ballot_sync(FULL_MASK, lane < n && my_ml != 0);
             while (pending) {
-                const int f = __ffs(pending) - 1;
-                const uint32_t W = __shfl_sync(FULL_MASK, my_mop, f);       // everything of THIS piece below W is final
-                const uint32_t ml_f = __shfl_sync(FULL_MASK, my_ml, f);
-                const bool in_ok = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
-                                   ((int)lane == f || (int64_t)my_mop + my_need <= (int64_t)W);
-                if (in_ok && !ext_ok) ext_ok = bits_ready(bits, xa, xb);
-                const bool ready = in_ok && ext_ok;
-                if (ready) {
-                    if (my_ext) { if (my_off >= my_ml) lane_copy_cg(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match_cg(dp + my_mop, my_off, my_ml); }
-                    else        { if (my_off >= my_ml) lane_copy(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match(dp + my_mop, my_off, my_ml); }
+                const bool mine = (pending >> lane) & 1u;
+                const bool small = my_ml <= LANE_CAP;
+                // a lane asks about short source windows itself; long ones (rare) are looked at by the whole warp, first one first
+                const bool ready = mine && my_span <= 256u && df_ready(c.df, xa, xb);
+                if (ready && small) {
+                    __threadfence_block();
+                    if (my_off >= my_ml) lane_copy(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match(dp + my_mop, my_off, my_ml);
                 }
-                const uint32_t rb = __ballot_sync(FULL_MASK, ready);
+                const uint32_t rb = __ballot_sync(FULL_MASK, ready && small);
+                uint32_t lb = __ballot_sync(FULL_MASK, ready && !small);     // long matches whose sources are there
+                const uint32_t wide = __ballot_sync(FULL_MASK, mine && my_span > 256u);
                 bool progressed = rb != 0u;
                 if (rb) {
-                    __threadfence();
-                    if (ready) bits_mark(bits, (uint64_t)(abs0 + my_mop), (uint64_t)(abs0 + my_mop) + my_ml);
+                    __threadfence_block();
+                    if (ready && small) df_mark(c.df, (uint64_t)(abs0 + my_mop), (uint64_t)(abs0 + my_mop) + my_ml);
                     pending &= ~rb;
                 }
-                if (ml_f > LANE_CAP) {                                      // the first pending match is a long one: whole warp
-                    const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
-                    const bool ext_f = off_f > W - piece_lo;
-                    const uint32_t span_f = ml_f < off_f ? ml_f : off_f;
-                    bool ok = true;
-                    if (ext_f) {
-                        const int64_t a = abs0 + (int64_t)W - (int64_t)off_f, e = a + span_f, l = abs0 + piece_lo;
-                        ok = bits_ready_warp(bits, a, e < l ? e : l, lane);
+                if (wide) {                                                 // one long source window per round: checked by all lanes
+                    const int g = __ffs(wide) - 1;
+                    const int64_t a = __shfl_sync(FULL_MASK, xa, g), e = __shfl_sync(FULL_MASK, xb, g);
+                    if (df_ready_warp(c.df, a, e, lane)) lb |= 1u << g;
+                }
+                while (lb) {                                                // long matches: the whole warp copies
+                    const int g = __ffs(lb) - 1; lb &= lb - 1;
+                    const uint32_t W = __shfl_sync(FULL_MASK, my_mop, g), ml_g = __shfl_sync(FULL_MASK, my_ml, g), off_g = __shfl_sync(FULL_MASK, my_off, g);
+                    __threadfence_block();
+                    if (off_g >= ml_g) group_copy_small(dp + W, dp + W - off_g, ml_g, lane, 32);
+                    else {                                                  // overlapping: period replication from the final window
+                        const uint8_t* m = dp + W - off_g; uint32_t r = lane % off_g; const uint32_t step = 32u % off_g;
+                        for (uint32_t i = lane; i < ml_g; i += 32) { dp[W + i] = m[r]; r += step; if (r >= off_g) r -= off_g; }
                     }
-                    if (ok) {
-                        __syncwarp();
-                        if (off_f >= ml_f) {
-                            if (ext_f) group_copy_cg(dp + W, dp + W - off_f, ml_f, lane, 32);
-                            else group_copy_small(dp + W, dp + W - off_f, ml_f, lane, 32);
-                        } else {                                            // overlapping: period replication from the final window
-                            const uint8_t* m = dp + W - off_f; uint32_t r = lane % off_f; const uint32_t step = 32u % off_f;
-                            for (uint32_t i = lane; i < ml_f; i += 32) { dp[W + i] = ext_f ? __ldcg(m + r) : m[r]; r += step; if (r >= off_f) r -= off_f; }
-                        }
-                        __threadfence();
-                        __syncwarp();
-                        bits_mark_warp(bits, (uint64_t)(abs0 + W), (uint64_t)(abs0 + W) + ml_f, lane);
-                        pending &= ~(1u << f);
-                        progressed = true;
-                    }
+                    __threadfence_block();
+                    __syncwarp();
+                    df_mark_warp(c.df, (uint64_t)(abs0 + W), (uint64_t)(abs0 + W) + ml_g, lane);
+                    pending &= ~(1u << g);
+                    progressed = true;
                 }
                 __syncwarp();
-                if (!progressed) __nanosleep(64);
+                if (!progressed) __nanosleep(32);
             }
         }
     }

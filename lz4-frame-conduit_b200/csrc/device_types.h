@@ -62,32 +62,39 @@ struct FrameIndex {
     uint32_t walk_pending;    // 1 = the serial walk over the block headers is left to the decoder kernel (2 = done there)
     uint32_t df;              // 1 = decoded by the dataflow kernels (decode_df.cu): no side information, any block mode
     uint32_t need_groups;     // dataflow workspace the scan wanted (groups of DF_G compressed bytes)
+    uint32_t need_tickets;    // ... and tickets (upper bound from the compressed sizes, exact after df_layout_kernel)
     FrameDesc desc;
 };
 
 // ---- dataflow decode (decode_df.cu)
-constexpr uint32_t DF_G = 1024u;            // compressed bytes per group = one chain table = (about) one piece
+constexpr uint32_t DF_G = 1024u;            // compressed bytes per group = one chain table
 constexpr uint32_t DF_LA = 96u;             // bytes behind a group its parse may look at (length runs longer than that: DF_SLOW)
 constexpr uint32_t DF_RUN = 64u;            // 255-bytes of one length field followed inside the table pass
-constexpr uint32_t DF_STORED_PIECE = 65536u;// a stored block is copied in pieces of this size
-struct DfHead { uint32_t exit, out; };      // chain from one position: where it leaves the group (kind in the top bits), bytes produced
-struct DfPiece { uint32_t block, tok, tok_end, out, out_end, flags, pad0, pad1; };   // block-relative token / output ranges
+constexpr uint32_t DF_BATCH = 32u;          // sequences per ticket (one per lane of the warp that decodes it)
+constexpr uint32_t DF_WIN_BYTES = 512u << 10;   // output window covered by the CTA's "final bytes" bitmap (64 KB of shared memory)
+constexpr uint32_t DF_WIN_MASK = DF_WIN_BYTES / 32u - 1u;
+constexpr uint32_t DF_HALF = DF_WIN_BYTES / 2u; // a ticket is handed out when its output ends within this much of the watermark
+constexpr uint32_t DF_RING = 128u;          // tickets between the lowest unfinished and the newest handed out (done flags)
+struct DfHead { uint32_t exit, out; };      // chain from one position of a group: packed (kind, sequences, where it leaves), bytes produced
+struct DfShared {                           // per-CTA dataflow state in shared memory (decode_df_kernel)
+    uint32_t* bits;                         // DF_WIN_BYTES / 32 words, circular: bit of output byte p is (p mod DF_WIN_BYTES)
+    volatile unsigned long long* final_below;   // every output byte below this buffer offset is final
+};
 struct DfState {
     unsigned long long bad_key;             // min over failures of (block << 8 | Err); all ones = none
     unsigned long long produced, total_out;
-    uint32_t n_pieces, ticket_links, ticket_decode, pad;
+    uint32_t n_tickets, n_units, ticket_links, ticket_units, ticket_tk, pad;
 };
-struct DfWork {                             // device workspaces of the dataflow path (all sized by the host from the scan's needs)
+struct DfWork {                             // device workspaces of the dataflow path (sized by the host from the scan's needs)
     uint32_t* grp_base;                     // [blocks + 1] first group of every block
     DfHead* heads;                          // [groups x DF_G]
     uint2* ent;                             // [groups] (first token, output offset) of the k-th group a block's chain enters
-    uint32_t* blk_nent; uint32_t* blk_usize;// [blocks]
-    uint32_t* piece_base;                   // [blocks + 1]
-    DfPiece* pieces;                        // [cap_pieces]
-    uint32_t* bits;                         // one bit per output byte
+    uint32_t* ent_seq;                      // [groups] ... and the number of that token's sequence within the block
+    uint32_t* blk_nent; uint32_t* blk_usize; uint32_t* blk_nseq;   // [blocks]
+    uint32_t* tk_base;                      // [blocks + 1] first ticket of every block
+    uint2* tk;                              // [cap_tickets] (token, output offset) of every DF_BATCH-th sequence of a block
     DfState* st;
-    uint32_t cap_groups, cap_pieces;
-    uint64_t bits_bytes;
+    uint32_t cap_groups, cap_tickets;
 };
 
 // Decode summary written by the finalise kernel

@@ -66,8 +66,8 @@ struct b2lz4_ctx {
     Small* d_small = nullptr;
     Small* h_small = nullptr;                     // pinned
     DevBuf scratch, subs, places, bplaces, blocks, pieces, chains, outs, stored, stage_in, stage_out, enc_tabs, ring, idx_frag, stage_in2, stage_out2;
-    DevBuf df_grp, df_heads, df_ent, df_nent, df_usize, df_pbase, df_pieces, df_bits;   // dataflow decode (decode_df.cu), allocated when a frame first needs them
-    uint32_t df_groups = 0, df_npieces = 0;       // their capacities
+    DevBuf df_grp, df_heads, df_ent, df_eseq, df_nent, df_usize, df_nseq, df_tkbase, df_tk;   // dataflow decode (decode_df.cu), allocated when a frame first needs them
+    uint32_t df_groups = 0, df_ntickets = 0;      // their capacities
     size_t ring_pos = 0; uint32_t ring_hist = 0;     // streaming linked-block decode: next output offset / valid history bytes
     b2lz4_stats stats{};
     char cuda_err[256] = {0};
@@ -213,6 +213,8 @@ size_t b2lz4_create(b2lz4_ctx** out, int device, const b2lz4_prefs* prefs) {
                                   (int)find_emit_smem_bytes())) != cudaSuccess) return fail(e, "cudaFuncSetAttribute");
     if ((e = cudaFuncSetAttribute(df_links_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)df_links_smem_bytes())) != cudaSuccess) return fail(e, "cudaFuncSetAttribute");
+    if ((e = cudaFuncSetAttribute(decode_df_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)decode_df_smem_bytes(32))) != cudaSuccess) return fail(e, "cudaFuncSetAttribute");
     *out = ctx;
     return 0;
 }
@@ -225,7 +227,7 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
                        &ctx->chains, &ctx->outs, &ctx->stored, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2,
-                       &ctx->df_grp, &ctx->df_heads, &ctx->df_ent, &ctx->df_nent, &ctx->df_usize, &ctx->df_pbase, &ctx->df_pieces, &ctx->df_bits }) b->release();
+                       &ctx->df_grp, &ctx->df_heads, &ctx->df_ent, &ctx->df_eseq, &ctx->df_nent, &ctx->df_usize, &ctx->df_nseq, &ctx->df_tkbase, &ctx->df_tk }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
@@ -385,6 +387,16 @@ size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* 
 // dataflow mode is on unless B2LZ4_DF=0 (then unindexed frames decode one warp per block, linked frames one warp per frame)
 static bool df_enabled() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_DF"); v = (e && *e == '0') ? 0 : 1; } return v == 1; }
 
+// warps per CTA of decode_df_kernel: B2LZ4_DF_WARPS, else by the size of the call (a guess at the number of units: the
+// host does not know the block size of a device-resident frame)
+static uint32_t df_cta_warps(const b2lz4_ctx* ctx, size_t n, size_t cap) {
+    static int env = -1;
+    if (env < 0) { const char* e = getenv("B2LZ4_DF_WARPS"); env = e ? atoi(e) : 0; }
+    if (env == 8 || env == 16 || env == 32) return (uint32_t)env;
+    (void)n;
+    return cap >= ((size_t)2 * ctx->sm_count << 22) ? 16u : 32u;      // >= two 4 MB blocks per SM: many units
+}
+
 static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, uint8_t* d_dst, size_t cap,
                                 uint32_t mode, uint32_t cap_tables, uint32_t hist)
 {
@@ -396,16 +408,18 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
             CU(ctx->df_grp.ensure(((size_t)cap_tables + 1) * sizeof(uint32_t)));
             CU(ctx->df_nent.ensure((size_t)cap_tables * sizeof(uint32_t)));
             CU(ctx->df_usize.ensure((size_t)cap_tables * sizeof(uint32_t)));
-            CU(ctx->df_pbase.ensure(((size_t)cap_tables + 1) * sizeof(uint32_t)));
+            CU(ctx->df_nseq.ensure((size_t)cap_tables * sizeof(uint32_t)));
+            CU(ctx->df_tkbase.ensure(((size_t)cap_tables + 1) * sizeof(uint32_t)));
             CU(ctx->df_heads.ensure((size_t)ctx->df_groups * DF_G * sizeof(DfHead)));
             CU(ctx->df_ent.ensure((size_t)ctx->df_groups * sizeof(uint2)));
-            CU(ctx->df_pieces.ensure((size_t)ctx->df_npieces * sizeof(DfPiece)));
-            CU(ctx->df_bits.ensure(cap / 8 + 64));
+            CU(ctx->df_eseq.ensure((size_t)ctx->df_groups * sizeof(uint32_t)));
+            CU(ctx->df_tk.ensure((size_t)ctx->df_ntickets * sizeof(uint2)));
         }
         W.grp_base = (uint32_t*)ctx->df_grp.p; W.heads = (DfHead*)ctx->df_heads.p; W.ent = (uint2*)ctx->df_ent.p;
-        W.blk_nent = (uint32_t*)ctx->df_nent.p; W.blk_usize = (uint32_t*)ctx->df_usize.p; W.piece_base = (uint32_t*)ctx->df_pbase.p;
-        W.pieces = (DfPiece*)ctx->df_pieces.p; W.bits = (uint32_t*)ctx->df_bits.p; W.st = &ctx->d_small->dfst;
-        W.cap_groups = ctx->df_groups; W.cap_pieces = ctx->df_npieces; W.bits_bytes = ctx->df_bits.cap;
+        W.ent_seq = (uint32_t*)ctx->df_eseq.p;
+        W.blk_nent = (uint32_t*)ctx->df_nent.p; W.blk_usize = (uint32_t*)ctx->df_usize.p; W.blk_nseq = (uint32_t*)ctx->df_nseq.p;
+        W.tk_base = (uint32_t*)ctx->df_tkbase.p; W.tk = (uint2*)ctx->df_tk.p; W.st = &ctx->d_small->dfst;
+        W.cap_groups = ctx->df_groups; W.cap_tickets = ctx->df_ntickets;
     }
     CU(ctx->blocks.ensure((size_t)cap_tables * sizeof(BlockRef)));
     CU(ctx->pieces.ensure((size_t)cap_tables * sizeof(Piece)));
@@ -429,8 +443,11 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
         B2_LAUNCH(df_links_kernel, ctx->sm_count * 3, DF_WARPS * 32, df_links_smem_bytes(), ctx->st, d_src, n, &ds->fi, bl, W);
         B2_LAUNCH(df_stitch_kernel, std::max(1u, std::min((cap_tables + 127u) / 128u, 1024u)), 128, 0, ctx->st, d_src, &ds->fi, bl, W);
         B2_LAUNCH(df_layout_kernel, 1, 256, 0, ctx->st, &ds->fi, (BlockRef*)ctx->blocks.p, cap, W);
-        B2_LAUNCH(df_pieces_kernel, ctx->sm_count * 4, 256, 0, ctx->st, &ds->fi, bl, W);
-        B2_LAUNCH(decode_df_kernel, ctx->sm_count * B2_DF_MINCTAS, DEC_WARPS * 32, 0, ctx->st, d_src, n, d_dst, cap, &ds->fi, bl, W, hist);
+        B2_LAUNCH(df_tickets_kernel, ctx->sm_count * 16, 128, 0, ctx->st, d_src, &ds->fi, bl, W);
+        // one CTA per unit (independent block / whole linked frame): 32 warps per CTA when there are few units (all the
+        // parallelism is inside them), 16 warps and two CTAs per SM when there are many
+        const uint32_t dfw = df_cta_warps(ctx, n, cap);
+        B2_LAUNCH(decode_df_kernel, ctx->sm_count * (32u / dfw), dfw * 32u, decode_df_smem_bytes(dfw), ctx->st, d_src, n, d_dst, cap, &ds->fi, bl, W, hist);
         launches += 5;
     }
     B2_LAUNCH(verify_block_checksums_kernel, std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st, 
@@ -467,9 +484,9 @@ static uint32_t tables_for(size_t n, size_t cap) {
 static void df_presize(b2lz4_ctx* ctx, size_t n, size_t cap) {
     if (!df_enabled()) return;
     if (ctx->prefs.use_index && !ctx->df_groups) return;
-    const uint64_t g = n / DF_G + tables_for(n, cap) + 16, p = g + cap / DF_STORED_PIECE + 16;
+    const uint64_t g = n / DF_G + tables_for(n, cap) + 16, t = n / (3u * DF_BATCH) + 2ull * tables_for(n, cap) + 16;
     if (g > ctx->df_groups) ctx->df_groups = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, g + g / 8);
-    if (p > ctx->df_npieces) ctx->df_npieces = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, p + p / 8);
+    if (t > ctx->df_ntickets) ctx->df_ntickets = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, t + t / 8);
 }
 // queues the first decode attempt on ctx->st without waiting; decompress_device_impl(..., launched0 = true) completes it
 static size_t decompress_begin(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, uint32_t hist, uint32_t mode0) {
@@ -506,7 +523,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
             if (fi.df) {
                 cap_tables = std::max(cap_tables, fi.need_blocks + 16);
                 ctx->df_groups = std::max(ctx->df_groups, fi.need_groups + 16);
-                ctx->df_npieces = std::max(ctx->df_npieces, fi.need_pieces + 16);
+                ctx->df_ntickets = std::max(ctx->df_ntickets, fi.need_tickets + 16);
             } else cap_tables = std::max(fi.need_blocks, fi.need_pieces) + 16;
             ++ctx->stats.retries; continue;
         }

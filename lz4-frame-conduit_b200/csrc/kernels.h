@@ -35,9 +35,6 @@ constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
 #define B2_DF_WARPS 8
 #endif
 constexpr int DF_WARPS = B2_DF_WARPS;            // warps per CTA in df_links_kernel (9.3 KB of shared memory each)
-#ifndef B2_DF_MINCTAS
-#define B2_DF_MINCTAS 4
-#endif
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
                   SCAN_DF = 32u,              // frames without a usable index go to the dataflow kernels (decode_df.cu)
                   SCAN_LEGACY = 8u,
@@ -63,7 +60,8 @@ __global__ void df_links_kernel(const uint8_t* src, uint64_t n_src, const FrameI
 size_t df_links_smem_bytes();
 __global__ void df_stitch_kernel(const uint8_t* src, const FrameIndex* fi, const BlockRef* blocks, DfWork W);
 __global__ void df_layout_kernel(FrameIndex* fi, BlockRef* blocks, uint64_t dst_cap, DfWork W);
-__global__ void df_pieces_kernel(const FrameIndex* fi, const BlockRef* blocks, DfWork W);
+__global__ void df_tickets_kernel(const uint8_t* src, const FrameIndex* fi, const BlockRef* blocks, DfWork W);
+size_t decode_df_smem_bytes(uint32_t warps);
 __global__ void decode_df_kernel(const uint8_t* src, uint64_t n_src, uint8_t* dst, uint64_t dst_cap,
                                  const FrameIndex* fi, const BlockRef* blocks, DfWork W, uint32_t hist);
 __global__ void df_finalize_kernel(const FrameIndex* fi, const uint32_t* block_crc_bad, DecodeResult* res, DfWork W);
