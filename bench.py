@@ -174,7 +174,7 @@ def run_reference(args):
     gen = load_gen()
     n = args.size_mib << 20
     threads = os.cpu_count() or 1
-    sample = min(n, max(64 << 20, (threads * 48) << 20))          # bounded: ~48 MiB per thread, <= the workload
+    sample = n                                                    # the whole stream of the workload (1 GiB: well under a second per step on all cores)
     buf = np.empty(sample, np.uint8)
     gen.b2gen_loglike(buf.ctypes.data, sample, 0x10C5)
     if lib is None:
@@ -190,14 +190,20 @@ def run_reference(args):
         tcs += tc; tds += td
     wall = time.perf_counter() - t0
     val = sample * args.steps / (tcs + tds) / 1e9
+    # the reference conduit is single-threaded (Conduit.hsc has no parallelism): its real figure, on a bounded sample
+    one = min(sample, 256 << 20)
+    tc1, td1, _ = ref_roundtrip(lib, buf.ctypes.data, one, 1)
     line = {"metric": METRIC, "value": val, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * (tcs + tds) / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": f"first {sample >> 20} MiB of the stream per step, {threads} slices"},
+            "config": {"workload": WORKLOAD, "bytes_per_gpu": n},
+            "reference_setup": f"whole {sample >> 20} MiB stream per step cut into {threads} independent slices, one reference conduit (linked 64 KB blocks) per host thread",
+            "one_thread": {"value": one / (tc1 + td1) / 1e9, "unit": UNIT, "compress_GBps": one / tc1 / 1e9, "decompress_GBps": one / td1 / 1e9,
+                           "sample": f"first {one >> 20} MiB, 1 thread: what the reference conduit really is"},
             "compress_GBps": sample * args.steps / tcs / 1e9, "decompress_GBps": sample * args.steps / tds / 1e9,
             "ratio": sample / csize,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "reference",
-                             "sample": f"{sample >> 20} MiB log-like, reference conduit replay (linked 64 KB blocks), {threads} threads on independent slices"},
+                             "sample": f"whole {sample >> 20} MiB log-like stream, reference conduit replay (linked 64 KB blocks), {threads} threads on independent slices"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "wall_s": wall}
     print(json.dumps(line))
@@ -251,6 +257,123 @@ def link_bandwidth(torch, n, barrier=None):
     return out
 
 
+def foreign_leg(torch, pkg, codec, lib, host_in, d_in, n):
+    """A frame this codec did not write: the reference library's own LZ4F output with the stock CLI's shape (4 MB independent
+    blocks, lz4io.c:159-175; no checksums), made on the host from the same stream.  Decompressed device-resident and end to
+    end.  No index: it goes through the dataflow kernels (csrc/decode_df.cu)."""
+    import numpy as np
+    if lib is None:
+        return None
+    lib.ref_frame_compress.restype = C.c_size_t
+    lib.ref_frame_compress.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t] + [C.c_int] * 6 + [C.c_size_t]
+    cap = n + n // 200 + (1 << 20)
+    host_f = torch.empty(cap, dtype=torch.uint8).pin_memory()
+    t0 = time.perf_counter()
+    fs = lib.ref_frame_compress(host_in.data_ptr(), n, host_f.data_ptr(), cap, 7, 1, 0, 0, 0, 1, 4 << 20)
+    t_make = time.perf_counter() - t0
+    if fs > (1 << 62):
+        return {"error": "reference library failed to make the frame"}
+    d_f = host_f[:fs].cuda()
+    d_o = torch.empty(n, dtype=torch.uint8, device="cuda")
+    best = None
+    for it in range(4):
+        r, used = codec.decompress_device(d_f.data_ptr(), fs, d_o.data_ptr(), n)
+        st = codec.stats()
+        assert r == n and used == fs
+        if it == 0:
+            assert torch.equal(d_o, d_in), "foreign frame: output differs"
+        elif best is None or st.ms_total < best.ms_total:
+            best = st
+    host_o = torch.empty(n, dtype=torch.uint8).pin_memory()
+    codec.decompress_host_ptr(host_f.data_ptr(), fs, host_o.data_ptr(), n)
+    t0 = time.perf_counter()
+    r, used = codec.decompress_host_ptr(host_f.data_ptr(), fs, host_o.data_ptr(), n)
+    t_host = time.perf_counter() - t0
+    ok = r == n and torch.equal(host_o, host_in)
+    return {"frame": "reference library LZ4F output, 4 MB independent blocks, no checksums, no index (the stock CLI's shape)",
+            "frame_bytes": fs, "ratio": n / fs, "made_on_host_s": t_make,
+            "decompress_GBps": n / (best.ms_total * 1e-3) / 1e9, "decode_kernels_ms": best.ms_main, "ms_total": best.ms_total,
+            "tickets": best.n_chains, "blocks": best.n_blocks,
+            "e2e_decompress_GBps": n / t_host / 1e9, "bit_exact": bool(ok)}
+
+
+def sharded_leg(torch, pkg, gen, n_dev, seg_mib=512):
+    """BASELINE.json configs 3 and 5 through ONE context whose host-buffer calls shard the blocks of ONE frame over n_dev
+    GPUs by block index (b2lz4_set_devices; no collective: blocks are independent) and reassemble them in order on the
+    host.  The stream is never resident: it is produced, compressed, decompressed and compared one pinned segment at a time
+    (b2lz4_compress_blocks_host / b2lz4_decompress_blocks_host; the frame header and EndMark are a few host-written bytes).
+    `frame_xxh32` is the XXH32 of the compressed frame: it must not depend on the number of devices."""
+    import numpy as np
+    try:
+        import xxhash
+    except Exception:
+        xxhash = None
+    lib = pkg.load()
+    seg = seg_mib << 20
+    out = {"n_devices": n_dev, "segment_mib": seg_mib,
+           "api": "b2lz4_set_devices + b2lz4_compress_blocks_host / b2lz4_decompress_blocks_host, pinned host segments"}
+    codec = pkg.Codec(0, block_size_id=7, sub_block_log2=17, write_index=0, use_index=0)
+    codec.set_devices(list(range(n_dev)))
+    cap = pkg.compress_bound(seg, codec.prefs)
+    h_in = torch.empty(seg, dtype=torch.uint8).pin_memory()
+    h_c = [torch.empty(cap, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    h_b = torch.empty(seg, dtype=torch.uint8).pin_memory()
+    info = pkg.FrameInfo()
+    hdr = pkg.frame_header_write(codec.prefs, 0)
+    lib.b2lz4_frame_header_parse(hdr, len(hdr), C.byref(info))
+    threads = min(16, os.cpu_count() or 1)
+
+    def fill_seg(kind, i):
+        if kind == "zeros":
+            if i == 0:
+                h_in.zero_()
+            return
+        per = seg // threads
+        fn = gen.b2gen_loglike if kind == "loglike" else gen.b2gen_random
+        ts = [threading.Thread(target=fn, args=(h_in.data_ptr() + k * per, per if k + 1 < threads else seg - k * per,
+                                                (0x10C5 + i) * 64 + k)) for k in range(threads)]
+        for t in ts: t.start()
+        for t in ts: t.join()
+
+    def stream(kind, gib):
+        nseg = (gib << 30) // seg
+        x = xxhash.xxh32() if xxhash else None
+        if x: x.update(hdr)
+        tc = td = 0.0; comp_total = len(hdr); ok = True
+        for i in range(nseg):
+            fill_seg(kind, i)
+            hc = h_c[i & 1]
+            flags = 1 if i == 0 else 0
+            t0 = time.perf_counter()
+            c = lib.b2lz4_compress_blocks_host(codec.h, h_in.data_ptr(), seg, hc.data_ptr(), cap, flags)
+            tc += time.perf_counter() - t0
+            if lib.b2lz4_is_error(c):
+                return {"error": lib.b2lz4_error_name(c).decode() + " (compress) " + lib.b2lz4_last_cuda_error(codec.h).decode()}
+            if x: x.update(memoryview(hc.numpy())[:c])
+            comp_total += c
+            t0 = time.perf_counter()
+            r = lib.b2lz4_decompress_blocks_host(codec.h, C.byref(info), hc.data_ptr(), c, h_b.data_ptr(), seg, flags)
+            td += time.perf_counter() - t0
+            if lib.b2lz4_is_error(r):
+                return {"error": lib.b2lz4_error_name(r).decode() + " (decompress) " + lib.b2lz4_last_cuda_error(codec.h).decode()}
+            ok = ok and r == seg and torch.equal(h_b, h_in)
+        end = C.create_string_buffer(8)
+        e = lib.b2lz4_frame_end(codec.h, end, 8)
+        if x: x.update(end.raw[:e])
+        comp_total += e
+        U = nseg * seg
+        return {"bytes": U, "frame_bytes": comp_total, "ratio": U / comp_total, "bit_exact": bool(ok),
+                "compress_GBps": U / tc / 1e9, "decompress_GBps": U / td / 1e9, "roundtrip_GBps": U / (tc + td) / 1e9,
+                "frame_xxh32": (x.intdigest() if x else None)}
+
+    stream("loglike", 1)                                              # warm-up: lanes on every device, workspaces, pinned staging
+    out["config3"] = dict(stream("loglike", 16), workload="ONE frame of 16 GiB log-like (> 2^32 bytes), 4 MB independent blocks, host in -> host out")
+    out["config5_random"] = dict(stream("random", 4), workload="4 GiB incompressible random: every block stored (lz4frame.c:749-752)")
+    out["config5_zeros"] = dict(stream("zeros", 4), workload="4 GiB zeros: one long overlapping match per block (lz4.c:425-456)")
+    codec.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -262,6 +385,8 @@ def main():
     ap.add_argument("--no-index", action="store_true", help="plain frames (drop-in default) instead of seekable ones")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-foreign", action="store_true", help="no foreign-frame (stock CLI shape) decompression leg")
+    ap.add_argument("--skip-sharded", action="store_true", help="no in-process multi-GPU leg (configs 3 and 5)")
     ap.add_argument("--workload", default="loglike", choices=sorted(WORKLOADS))
     ap.add_argument("--block-id", type=int, default=7, help="frame block size id 4..7 = 64 KB .. 4 MB")
     args = ap.parse_args()
@@ -278,8 +403,10 @@ def main():
         print("bench.py: no CUDA device — this benchmark has no CPU path", file=sys.stderr)
         return 2
     torch.cuda.set_device(local)
+    side = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        side = dist.new_group(backend="gloo")       # host-side barrier for the leg where only rank 0 works (an NCCL barrier spins on the GPUs)
 
     pkg = importlib.import_module("lz4-frame-conduit_b200")
     gen = load_gen()
@@ -369,6 +496,33 @@ def main():
                         "note": "pinned copies, all ranks at once, slowest rank", "bound_GBps": world * n / (bound_ms * 1e-3) / 1e9,
                         "frac": (world * n / (e_ms * 1e-3)) / (world * n / (bound_ms * 1e-3))}}
 
+    # ---- a frame this codec did not write (rank 0 only; the other ranks wait at the barrier below)
+    foreign = None
+    if rank == 0 and not args.skip_foreign and args.workload == "loglike":
+        try:
+            foreign = foreign_leg(torch, pkg, codec, ref_lib(), host_in, d_in, n)
+        except Exception as ex:                                   # reported, never fatal for the headline line
+            foreign = {"error": repr(ex)}
+
+    # ---- configs 3 and 5: ONE frame's blocks sharded over all GPUs of the job inside ONE process (rank 0); the other
+    # ranks have freed their buffers and wait
+    sharded = None
+    if not args.skip_sharded and args.workload == "loglike":
+        del d_comp, d_back
+        if rank != 0:
+            del d_in
+        torch.cuda.empty_cache()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=side)
+        if rank == 0:
+            try:
+                sharded = sharded_leg(torch, pkg, gen, world)
+            except Exception as ex:
+                sharded = {"error": repr(ex)}
+        if world > 1:
+            dist.barrier(group=side)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -415,7 +569,7 @@ def main():
                        "l2": "inputs larger than L2 (1 GiB stream vs 126 MB L2)", "parallelism": f"{world} independent streams, no collective"},
             "compress_GBps": world * n / (c_ms * 1e-3) / 1e9, "decompress_GBps": world * n / (d_ms * 1e-3) / 1e9,
             "device_ms_per_step": dev_ms, "ratio": n / csize, "compressed_bytes": csize,
-            "roofline": dominant, "roofline_other": other, "cpu_baseline": cpu, "e2e": e2e,
+            "roofline": dominant, "roofline_other": other, "cpu_baseline": cpu, "e2e": e2e, "foreign": foreign, "sharded": sharded,
             "gpu_launches": ev["launches"], "clocks": clocks}
     if cpu:
         line["ratio_vs_reference_default"] = (n / csize) / cpu["ratio"]

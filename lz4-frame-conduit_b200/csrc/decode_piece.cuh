@@ -120,6 +120,12 @@ __device__ __forceinline__ void lane_match(uint8_t* d, uint32_t off, uint32_t n)
     for (; k < n; ++k) { d[k] = s[r]; r = (r + 1 == off) ? 0u : r + 1; }
 }
 
+// ... the window being [s, s + off) anywhere (a chased source, decode_piece's dataflow branch)
+__device__ __forceinline__ void lane_match_from(uint8_t* d, const uint8_t* s, uint32_t off, uint32_t n) {
+    uint32_t r = 0;
+    for (uint32_t k = 0; k < n; ++k) { d[k] = s[r]; r = (r + 1 == off) ? 0u : r + 1; }
+}
+
 // Warp-cooperative match copy (long matches): the source window [d - off, d) is final.
 //   off >= ml            plain copy
 //   16 % off == 0        (run-length style: 1, 2, 4, 8, 16) every aligned 16-byte chunk of the run holds the same
@@ -453,8 +459,34 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
             // are set — it waits for nothing else, and nothing waits for it but the matches that really read it.
             const uint32_t my_mop = my_op + my_ll;
             const uint32_t my_span = my_ml < my_off ? my_ml : my_off;       // bytes of the source window that are read
-            const int64_t xa = abs0 + (int64_t)my_mop - (int64_t)my_off, xb = xa + my_span;
+            int64_t xa = abs0 + (int64_t)my_mop - (int64_t)my_off;          // the source window, in buffer coordinates: [xa, xa + span)
             uint32_t pending = __ballot_sync(FULL_MASK, lane < n && my_ml != 0);
+            // ---- source chasing inside the batch: a match that reads nothing but the output of an EARLIER, still pending,
+            // non-overlapping match of this batch reads that match's source instead (the bytes are the same).  Log-like data is
+            // full of "this line's field = the previous line's field = the line before's ...": without this every link of
+            // such a chain costs a round trip through memory; with it the lanes follow the chain back with shuffles.
+            {
+                const uint32_t key = lane < n ? my_op : 0xFFFFFFFFu;          // sequence starts, ascending over the lanes
+                const uint32_t plain = __ballot_sync(FULL_MASK, lane < n && my_ml != 0 && my_off >= my_ml);
+                for (int it = 0; it < 6; ++it) {
+                    const int64_t sa = xa - abs0;                              // block-relative start of my source
+                    uint32_t lo = 0;
+                    #pragma unroll
+                    for (uint32_t st = 16u; st; st >>= 1) {                    // last lane whose sequence starts at or below sa
+                        const uint32_t cand = lo + st;
+                        const uint32_t v = __shfl_sync(FULL_MASK, key, cand & 31u);
+                        if (cand < 32u && (int64_t)v <= sa) lo = cand;
+                    }
+                    const uint32_t i_mop = __shfl_sync(FULL_MASK, my_mop, lo), i_ml = __shfl_sync(FULL_MASK, my_ml, lo);
+                    const int64_t i_xa = __shfl_sync(FULL_MASK, xa, lo);
+                    const bool hop = ((pending >> lane) & 1u) && sa >= (int64_t)op0 && lo < lane && ((pending & plain) >> lo & 1u) &&
+                                     sa >= (int64_t)i_mop && sa + (int64_t)my_span <= (int64_t)i_mop + (int64_t)i_ml;
+                    if (hop) xa = i_xa + (sa - (int64_t)i_mop);
+                    if (!__any_sync(FULL_MASK, hop)) break;
+                }
+            }
+            const int64_t xb = xa + my_span;
+            const uint8_t* const my_src = dp + (xa - abs0);
             while (pending) {
                 const bool mine = (pending >> lane) & 1u;
                 const bool small = my_ml <= LANE_CAP;
@@ -462,7 +494,7 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 const bool ready = mine && my_span <= 256u && df_ready(c.df, xa, xb);
                 if (ready && small) {
                     __threadfence_block();
-                    if (my_off >= my_ml) lane_copy(dp + my_mop, dp + my_mop - my_off, my_ml); else lane_match(dp + my_mop, my_off, my_ml);
+                    if (my_off >= my_ml) lane_copy(dp + my_mop, my_src, my_ml); else lane_match_from(dp + my_mop, my_src, my_off, my_ml);
                 }
                 const uint32_t rb = __ballot_sync(FULL_MASK, ready && small);
                 uint32_t lb = __ballot_sync(FULL_MASK, ready && !small);     // long matches whose sources are there
@@ -481,10 +513,11 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 while (lb) {                                                // long matches: the whole warp copies
                     const int g = __ffs(lb) - 1; lb &= lb - 1;
                     const uint32_t W = __shfl_sync(FULL_MASK, my_mop, g), ml_g = __shfl_sync(FULL_MASK, my_ml, g), off_g = __shfl_sync(FULL_MASK, my_off, g);
+                    const uint8_t* m = dp + (__shfl_sync(FULL_MASK, xa, g) - abs0);
                     __threadfence_block();
-                    if (off_g >= ml_g) group_copy_small(dp + W, dp + W - off_g, ml_g, lane, 32);
+                    if (off_g >= ml_g) group_copy_small(dp + W, m, ml_g, lane, 32);
                     else {                                                  // overlapping: period replication from the final window
-                        const uint8_t* m = dp + W - off_g; uint32_t r = lane % off_g; const uint32_t step = 32u % off_g;
+                        uint32_t r = lane % off_g; const uint32_t step = 32u % off_g;
                         for (uint32_t i = lane; i < ml_g; i += 32) { dp[W + i] = m[r]; r += step; if (r >= off_g) r -= off_g; }
                     }
                     __threadfence_block();

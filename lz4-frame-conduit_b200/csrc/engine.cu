@@ -385,7 +385,9 @@ size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* 
 
 // -------------------------------------------------------------------------------------- decompress
 // dataflow mode is on unless B2LZ4_DF=0 (then unindexed frames decode one warp per block, linked frames one warp per frame)
-static bool df_enabled() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_DF"); v = (e && *e == '0') ? 0 : 1; } return v == 1; }
+static int df_level() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_DF"); v = !e ? 1 : (*e == '0') ? 0 : (*e == '2') ? 2 : 1; } return v; }
+static bool df_enabled() { return df_level() != 0; }
+static uint32_t df_mode() { return df_level() == 0 ? 0u : df_level() == 2 ? (SCAN_DF | SCAN_DF_ALL) : SCAN_DF; }
 
 // warps per CTA of decode_df_kernel: B2LZ4_DF_WARPS, else by the size of the call (a guess at the number of units: the
 // host does not know the block size of a device-resident frame)
@@ -491,7 +493,7 @@ static void df_presize(b2lz4_ctx* ctx, size_t n, size_t cap) {
 // queues the first decode attempt on ctx->st without waiting; decompress_device_impl(..., launched0 = true) completes it
 static size_t decompress_begin(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, uint32_t hist, uint32_t mode0) {
     ctx->stats = b2lz4_stats{};
-    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK | (df_enabled() ? SCAN_DF : 0u);
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK | df_mode();
     df_presize(ctx, n, cap);
     return decompress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, mode, tables_for(n, cap), hist);
 }
@@ -508,7 +510,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
     static uint8_t* dummy = nullptr;
     uint8_t* dst = (uint8_t*)d_dst;
     if (!dst) { if (!dummy) CU(cudaMalloc(&dummy, 256)); dst = dummy; }
-    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK | (df_enabled() ? SCAN_DF : 0u);
+    uint32_t mode = mode0 | (ctx->prefs.use_index ? SCAN_USE_INDEX : 0u) | SCAN_OVERLAP_WALK | df_mode();
     uint32_t cap_tables = tables_for(n, cap);
     if (!launched0) df_presize(ctx, n, cap);
     for (int attempt = 0; attempt < 4; ++attempt) {
@@ -537,8 +539,10 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
         if (fi.err == OK && !fi.layout_known && fi.n_chains > 1 && !(mode & SCAN_SINGLE_CHAIN) &&
             (dr.err != OK || !dr.layout_ok) && attempt < 3) {
             // the "block b starts at b * blockSize" layout did not hold (a middle block decoded short: flushed
-            // stream) or an error may stem from it: redo with the blocks chained in order, which is exact
-            mode = (mode & ~SCAN_USE_INDEX) | SCAN_SINGLE_CHAIN;
+            // stream) or an error may stem from it: redo with the exact layout — the dataflow path computes every block's
+            // decoded size before it copies a byte (without it: the blocks chained in order by one warp)
+            mode = (mode & ~SCAN_USE_INDEX) | (df_enabled() ? (SCAN_DF | SCAN_DF_ALL) : SCAN_SINGLE_CHAIN);
+            if (df_enabled() && !ctx->df_groups) { const uint32_t keep = ctx->prefs.use_index; ctx->prefs.use_index = 0; df_presize(ctx, n, cap); ctx->prefs.use_index = keep; }
             ++ctx->stats.retries; continue;
         }
         float a = 0, b = 0, c = 0;

@@ -36,7 +36,8 @@ constexpr int LAYOUT_THREADS = 256;   // layout_kernel's single CTA
 #endif
 constexpr int DF_WARPS = B2_DF_WARPS;            // warps per CTA in df_links_kernel (9.3 KB of shared memory each)
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
-                  SCAN_DF = 32u,              // frames without a usable index go to the dataflow kernels (decode_df.cu)
+                  SCAN_DF = 32u,              // frames without a usable index may go to the dataflow kernels (decode_df.cu)
+                  SCAN_DF_ALL = 64u,          // ... whatever their block size (B2LZ4_DF=2; the exact-layout retry)
                   SCAN_LEGACY = 8u,
                   SCAN_OVERLAP_WALK = 16u };  // plain independent-block frames: walk the block headers inside the decoder kernel   // blocks of a legacy frame (lz4_Frame_format.md:338-386): 8 MB, always compressed, no flag bit
 constexpr uint32_t LEGACY_BLOCK = 8u << 20;
