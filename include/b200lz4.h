@@ -38,7 +38,10 @@ typedef struct {
                                    entry points, lets the decoder run every sub-block in parallel).  Default 0: the
                                    stock lz4 CLI skips skippable frames in files but fails on pipes (lz4io.c:1124-1133). */
     uint32_t use_index;         /* decoder: 1 = trust-but-verify a trailing B2IX index frame */
-    uint32_t reserved;
+    uint32_t block_linked;      /* 1 = linked blocks (LZ4F_blockLinked, the reference conduit's own mode, Conduit.hsc:248-263): matches
+                                   reach up to 64 KB back across block borders — 64 KB blocks then compress like the reference's.
+                                   Such frames carry no index (write_index is ignored); a dictionary (b2lz4_set_dict) is used by
+                                   linked frames only. */
 } b2lz4_prefs;
 
 typedef struct {                /* parsed frame header (replaces LZ4F_getFrameInfo, lz4frame.c:1246-1281) */
@@ -76,6 +79,12 @@ void   b2lz4_default_prefs(b2lz4_prefs* prefs);
  * reassembles the output in block order.  No collective is involved — independent blocks have no exchange step.
  * n = 0 returns to the context's own device.  The frame bytes do not depend on the device list. */
 size_t b2lz4_set_devices(b2lz4_ctx* ctx, const int* devices, int n);
+/* Dictionary (replaces LZ4F_createCDict + LZ4F_compressBegin_usingCDict / LZ4F_decompress_usingDict, lz4/lib/lz4frame.c:478-521,
+ * 594-702, 1842-1860): the bytes are treated as stream history in front of the first block of every frame that follows.  Only the
+ * last 64 KB matter and are kept (copied).  Linked-block frames only (prefs.block_linked on the compress side; on the decompress side
+ * a match of an INDEPENDENT block that reaches into the dictionary is reported as ERROR_decompressionFailed).  dict_id != 0 is
+ * written into the frame header (lz4frame.c:692-695).  n = 0 removes the dictionary. */
+size_t b2lz4_set_dict(b2lz4_ctx* ctx, const void* dict, size_t n, uint32_t dict_id);
 int    b2lz4_device_count(void);
 
 /* ---- sizes (replaces LZ4F_compressBound / LZ4F_compressFrameBound, lz4frame.c:324-349, 370-381) */
@@ -87,6 +96,7 @@ size_t b2lz4_decompress_bound(const void* src, size_t n);
 
 /* ---- host-only frame helpers: no GPU involved (replace lz4frame.c:663-701 and :1109-1198) */
 size_t b2lz4_frame_header_write(void* dst, size_t cap, const b2lz4_prefs* prefs, uint64_t content_size);
+size_t b2lz4_frame_header_write2(void* dst, size_t cap, const b2lz4_prefs* prefs, uint64_t content_size, uint32_t dict_id);
 size_t b2lz4_frame_header_parse(const void* src, size_t n, b2lz4_frame_info* info);   /* returns header size */
 
 /* ---- one LZ4 frame, buffers resident in device memory (config 2).  Return the frame size / the decoded

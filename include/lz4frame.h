@@ -85,6 +85,7 @@ typedef struct LZ4F_cctx_s LZ4F_cctx;
 typedef LZ4F_cctx* LZ4F_compressionContext_t;
 typedef struct LZ4F_dctx_s LZ4F_dctx;
 typedef LZ4F_dctx* LZ4F_decompressionContext_t;
+typedef struct LZ4F_CDict_s LZ4F_CDict;
 
 unsigned    LZ4F_isError(LZ4F_errorCode_t code);
 const char* LZ4F_getErrorName(LZ4F_errorCode_t code);
@@ -105,6 +106,17 @@ size_t LZ4F_getFrameInfo(LZ4F_dctx* dctx, LZ4F_frameInfo_t* frameInfoPtr, const 
 size_t LZ4F_decompress(LZ4F_dctx* dctx, void* dstBuffer, size_t* dstSizePtr,
                        const void* srcBuffer, size_t* srcSizePtr, const LZ4F_decompressOptions_t* dOptPtr);
 void   LZ4F_resetDecompressionContext(LZ4F_dctx* dctx);
+
+/* Dictionaries (the reference lists them as TODO, Conduit.hsc:21-23; lz4/lib/lz4frame.h:530-607, lz4frame.c:478-521, 594-702,
+ * 1842-1860).  A dictionary is stream history in front of the first block: it is used by LINKED-block frames, which
+ * LZ4F_compressBegin_usingCDict writes whenever prefs->frameInfo.blockMode says so (LZ4F_blockLinked is the zero value).
+ * Plain LZ4F_compressBegin keeps writing independent blocks unless B2LZ4_BLOCK_MODE=honour is set in the environment. */
+LZ4F_CDict* LZ4F_createCDict(const void* dictBuffer, size_t dictSize);
+void        LZ4F_freeCDict(LZ4F_CDict* CDict);
+size_t LZ4F_compressBegin_usingCDict(LZ4F_cctx* cctx, void* dstBuffer, size_t dstCapacity, const LZ4F_CDict* cdict,
+                                     const LZ4F_preferences_t* prefsPtr);
+size_t LZ4F_decompress_usingDict(LZ4F_dctx* dctx, void* dstBuffer, size_t* dstSizePtr, const void* srcBuffer, size_t* srcSizePtr,
+                                 const void* dict, size_t dictSize, const LZ4F_decompressOptions_t* decompressOptionsPtr);
 
 #ifdef __cplusplus
 }

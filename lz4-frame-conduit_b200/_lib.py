@@ -14,7 +14,7 @@ class Prefs(C.Structure):
     """b2lz4_prefs — see include/b200lz4.h (mirrors Preferences/FrameInfo of CTypes.hsc:155-232)."""
     _fields_ = [(n, C.c_uint32) for n in (
         "block_size_id", "block_checksum", "content_checksum", "content_size",
-        "sub_block_log2", "write_index", "use_index", "reserved")]
+        "sub_block_log2", "write_index", "use_index", "block_linked")]
 
 
 class FrameInfo(C.Structure):
@@ -42,6 +42,8 @@ SYMBOLS = {
     "b2lz4_destroy": (_sz, [_vp]),
     "b2lz4_set_prefs": (_sz, [_vp, C.POINTER(Prefs)]),
     "b2lz4_set_devices": (_sz, [_vp, C.POINTER(C.c_int), C.c_int]),
+    "b2lz4_set_dict": (_sz, [_vp, _vp, _sz, C.c_uint32]),
+    "b2lz4_frame_header_write2": (_sz, [_vp, _sz, C.POINTER(Prefs), C.c_uint64, C.c_uint32]),
     "b2lz4_default_prefs": (None, [C.POINTER(Prefs)]),
     "b2lz4_device_count": (C.c_int, []),
     "b2lz4_compress_bound": (_sz, [_sz, C.POINTER(Prefs)]),

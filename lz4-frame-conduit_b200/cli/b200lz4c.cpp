@@ -7,6 +7,8 @@
 // `decompress` (Conduit.hsc:598-701): LZ4F_decompress until it returns 0, "stream ended before EndMark" otherwise.
 // Beyond the reference program:
 //   -B4..-B7, --block-checksum, --content-checksum   the Preferences the conduit API cannot reach (Conduit.hsc:347)
+//   -BD              linked blocks (blockMode = linked taken literally: matches cross block borders, like `lz4 -BD`)
+//   -D FILE          dictionary (LZ4F_compressBegin_usingCDict / LZ4F_decompress_usingDict; frames become linked-block frames)
 //   --all-frames     decode every concatenated frame, skip skippable frames, decode legacy frames — what `lz4 -d`
 //                    does (lz4/programs/lz4io.c:1094-1135, 895-940); default = first frame only, like the conduit
 // All codec work happens on the GPU inside the library; this file only moves bytes between files and the C ABI.
@@ -50,11 +52,16 @@ struct Reader {                               // buffered input with look-ahead
 
 uint32_t le32(const uint8_t* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }
 
-void do_compress(FILE* in, FILE* out, const LZ4F_preferences_t& prefs) {
+std::vector<uint8_t> g_dict; bool g_have_dict = false;
+
+void do_compress(FILE* in, FILE* out, const LZ4F_preferences_t& prefs, bool literal_mode) {
     LZ4F_cctx* c = nullptr;
     check(LZ4F_createCompressionContext(&c, LZ4F_VERSION));
     const size_t CHUNK = 4u << 20;
     std::vector<uint8_t> ibuf(CHUNK), obuf(check(LZ4F_compressBound(CHUNK, &prefs)) + LZ4F_HEADER_SIZE_MAX);
+    LZ4F_CDict* cd = g_have_dict ? LZ4F_createCDict(g_dict.data(), g_dict.size()) : nullptr;
+    if (literal_mode) put(out, obuf.data(), check(LZ4F_compressBegin_usingCDict(c, obuf.data(), obuf.size(), cd, &prefs)));
+    else
     put(out, obuf.data(), check(LZ4F_compressBegin(c, obuf.data(), obuf.size(), &prefs)));
     for (;;) {
         size_t n = fread(ibuf.data(), 1, CHUNK, in);
@@ -63,6 +70,7 @@ void do_compress(FILE* in, FILE* out, const LZ4F_preferences_t& prefs) {
     }
     put(out, obuf.data(), check(LZ4F_compressEnd(c, obuf.data(), obuf.size(), nullptr)));
     check(LZ4F_freeCompressionContext(c));
+    LZ4F_freeCDict(cd);
 }
 
 // one legacy frame (after its magic): [u32 size][LZ4 block]... until EOF or a word that cannot be a block size
@@ -127,7 +135,8 @@ void do_decompress(FILE* in, FILE* out, bool all_frames) {
                 if (skippable) die("skippable frame: truncated");
                 die("decompress: stream ended before EndMark"); } }                            // Conduit.hsc:689
             size_t ssz = rd.avail(), dsz = obuf.size();
-            hint = check(LZ4F_decompress(d, obuf.data(), &dsz, rd.ptr(), &ssz, nullptr));
+            hint = check(g_have_dict ? LZ4F_decompress_usingDict(d, obuf.data(), &dsz, rd.ptr(), &ssz, g_dict.data(), g_dict.size(), nullptr)
+                                     : LZ4F_decompress(d, obuf.data(), &dsz, rd.ptr(), &ssz, nullptr));
             put(out, obuf.data(), dsz);
             rd.consume(ssz);
             if (hint > obuf.size() && hint < (1ull << 31)) obuf.resize(hint);
@@ -143,18 +152,26 @@ void do_decompress(FILE* in, FILE* out, bool all_frames) {
 
 int main(int argc, char** argv) {
     const char* in_path = nullptr; const char* out_path = nullptr;
-    bool decompress = false, all_frames = false;
+    bool decompress = false, all_frames = false, literal_mode = false;
     LZ4F_preferences_t prefs; memset(&prefs, 0, sizeof prefs);
     int npos = 0;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         if (a == "-d" || a == "--decompress") decompress = true;
         else if (a == "--all-frames") all_frames = true;
+        else if (a == "-BD") { prefs.frameInfo.blockMode = LZ4F_blockLinked; literal_mode = true; }
+        else if (a == "-D") {
+            if (++i >= argc) die("-D needs a file");
+            FILE* f = fopen(argv[i], "rb"); if (!f) die(std::string("cannot open dictionary ") + argv[i]);
+            uint8_t tmp[65536]; size_t k;
+            while ((k = fread(tmp, 1, sizeof tmp, f)) > 0) g_dict.insert(g_dict.end(), tmp, tmp + k);
+            fclose(f); g_have_dict = true; literal_mode = true;
+        }
         else if (a.size() == 3 && a[0] == '-' && a[1] == 'B' && a[2] >= '4' && a[2] <= '7') prefs.frameInfo.blockSizeID = (LZ4F_blockSizeID_t)(a[2] - '0');
         else if (a == "--block-checksum" || a == "-BX") prefs.frameInfo.blockChecksumFlag = LZ4F_blockChecksumEnabled;
         else if (a == "--content-checksum") prefs.frameInfo.contentChecksumFlag = LZ4F_contentChecksumEnabled;
         else if (a == "-h" || a == "--help") {
-            printf("Usage: b200lz4c [INPUT_FILE] [OUTPUT-FILE] [-d|--decompress] [-B4..-B7] [--block-checksum] [--content-checksum] [--all-frames]\n"
+            printf("Usage: b200lz4c [INPUT_FILE] [OUTPUT-FILE] [-d|--decompress] [-B4..-B7] [--block-checksum] [--content-checksum] [-BD] [-D DICT_FILE] [--all-frames]\n"
                    "  Compress or decompress .lz4 files\n");
             return 0;
         }
@@ -166,7 +183,7 @@ int main(int argc, char** argv) {
     FILE* out = (!out_path || !strcmp(out_path, "-")) ? stdout : fopen(out_path, "wb");
     if (!out) die(std::string("cannot open ") + out_path);
     setvbuf(out, nullptr, _IOFBF, 4u << 20);
-    if (decompress) do_decompress(in, out, all_frames); else do_compress(in, out, prefs);
+    if (decompress) do_decompress(in, out, all_frames); else do_compress(in, out, prefs, literal_mode);
     if (fflush(out) != 0) die("write error");
     if (out != stdout) fclose(out);
     if (in != stdin) fclose(in);

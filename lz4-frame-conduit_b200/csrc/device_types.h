@@ -120,6 +120,8 @@ struct EncParams {
     uint32_t content_checksum;
     uint32_t write_header;    // 1 = emit frame header (+ EndMark, checksum slot, index) around the blocks
     uint32_t write_index;     // 1 = append the B2IX skippable index frame
+    uint32_t linked;          // 1 = linked blocks: a match may reach up to 65535 bytes back across block borders (lz4_Frame_format.md:155-163)
+    uint32_t hist;            // bytes of earlier stream (or dictionary) that lie directly in front of src in device memory
     FrameDesc desc;
 };
 

@@ -156,14 +156,20 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 
         const uint32_t blk = s / P.subs_per_block, j = s - blk * P.subs_per_block;
         const uint64_t blk_start = (uint64_t)blk * P.block_size;
-        const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
-        // the warp parses the unit [b0, b1); its matches may reach back to d0, the start of the match domain the unit
-        // belongs to (dom_units units = the piece ONE decoder warp decodes, so nothing may reach before it)
-        const uint32_t b0 = j * P.sub_size;
+        // linked blocks (and dictionaries, LZ4F_compressBegin_usingCDict, lz4frame.c:594-702): the bytes in front of the block
+        // — earlier blocks of the stream, the dictionary in front of the first one — are part of the match domain.  Every
+        // position below is counted from `base`, which then lies hb bytes in front of the block.
+        uint32_t hb = 0;
+        if (P.linked) { const uint64_t h = blk_start + P.hist; hb = h > 65536ull ? 65536u : (uint32_t)h; }
+        const uint32_t usize = hb + (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
+        // the warp parses the unit [b0, b1); its matches may reach back to d0: the start of the match domain the unit
+        // belongs to (dom_units units = the piece ONE decoder warp decodes, so nothing may reach before it), or — linked —
+        // 64 KB in front of the unit wherever that lies
+        const uint32_t b0 = hb + j * P.sub_size;
         const uint32_t b1 = (b0 + P.sub_size < usize) ? b0 + P.sub_size : usize;
-        const uint32_t d0 = (j / P.dom_units) * P.dom_units * P.sub_size;
+        const uint32_t d0 = P.linked ? (b0 > 65536u ? b0 - 65536u : 0u) : (j / P.dom_units) * P.dom_units * P.sub_size;
         const bool last_sub = (b1 == usize);
-        const uint8_t* __restrict__ base = src + blk_start;
+        const uint8_t* __restrict__ base = src + blk_start - hb;
         uint8_t* out = scratch + (uint64_t)s * P.scratch_stride;
 
         // zero the table so the parse is deterministic, then prime it with the part of the domain in front of the unit:
@@ -217,11 +223,11 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 
         // positions that may start a match: p + 4 <= b1 and p <= usize - 12 (block end rule)
         uint32_t limit = 0;
-        if (usize >= 13u) {
+        if (usize - hb >= 13u) {                                    // (the block's own size decides: lz4_Block_format.md:108-129)
             uint32_t la = b1 >= 3u ? b1 - 3u : 0u, lb = usize - 11u;
             limit = la < lb ? la : lb;
         }
-        const uint32_t matchlimit = (usize >= 5u) ? ((b1 < usize - 5u) ? b1 : usize - 5u) : 0u;
+        const uint32_t matchlimit = (usize - hb >= 5u) ? ((b1 < usize - 5u) ? b1 : usize - 5u) : 0u;
 
         uint32_t ip = b0, anchor = b0, o = 0, T0 = b0;
         uint32_t miss = 0, nseq = 0, first_ll = 0, first_hdr = 0, npend = 0;

@@ -85,7 +85,13 @@ struct b2lz4_ctx {
     XxhState* h_xxh = nullptr;
     bool sum_host = false;                        // the running content checksum of the current frame lives in h_xxh
     uint8_t* h_frag = nullptr; size_t h_frag_cap = 0;   // pinned: index fragments of the chunks
+    // dictionary (LZ4F_createCDict / LZ4F_decompress_usingDict, lz4frame.c:478-521, 1842-1860): its last 64 KB, what a
+    // block can reach (lz4_Frame_format.md:226-240).  Used by linked-block frames, on both sides.
+    std::vector<uint8_t> dict; uint32_t dict_id = 0;
+    std::vector<uint8_t> tail;                    // linked-block streaming compression: the last 64 KB of the batches so far
+    DevBuf dict_stage;
 };
+constexpr size_t HIST_MAX = 65536;
 
 namespace {
 
@@ -98,7 +104,7 @@ namespace {
 void fill_desc(const b2lz4_prefs& p, FrameDesc& d, uint64_t content_size) {
     memset(&d, 0, sizeof d);
     d.block_size_id = p.block_size_id ? p.block_size_id : 7u;
-    d.block_independent = 1;
+    d.block_independent = p.block_linked ? 0u : 1u;
     d.block_checksum = p.block_checksum ? 1u : 0u;
     d.content_checksum = p.content_checksum ? 1u : 0u;
     // like the reference, the field is only emitted for a non-zero size (lz4frame.c:679, 686-690)
@@ -170,6 +176,15 @@ size_t b2lz4_frame_header_write(void* dst, size_t cap, const b2lz4_prefs* prefs,
     return header_write((uint8_t*)dst, d);
 }
 
+size_t b2lz4_frame_header_write2(void* dst, size_t cap, const b2lz4_prefs* prefs, uint64_t content_size, uint32_t dict_id) {
+    b2lz4_prefs p; if (prefs) p = *prefs; else b2lz4_default_prefs(&p);
+    if (!prefs_valid(p)) return err_code(E_maxBlockSize_invalid);
+    if (cap < (size_t)HEADER_MAX) return err_code(E_dstMaxSize_tooSmall);
+    FrameDesc d; fill_desc(p, d, content_size);
+    if (dict_id) { d.has_dict_id = 1; d.dict_id = dict_id; }
+    return header_write((uint8_t*)dst, d);
+}
+
 size_t b2lz4_frame_header_parse(const void* src, size_t n, b2lz4_frame_info* info) {
     FrameDesc d{};
     Err e = header_parse((const uint8_t*)src, n, d);
@@ -227,7 +242,7 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->st2) cudaStreamSynchronize(ctx->st2);
     for (DevBuf* b : { &ctx->scratch, &ctx->subs, &ctx->places, &ctx->bplaces, &ctx->blocks, &ctx->pieces,
                        &ctx->chains, &ctx->outs, &ctx->stored, &ctx->stage_in, &ctx->stage_out, &ctx->enc_tabs, &ctx->ring, &ctx->idx_frag, &ctx->stage_in2, &ctx->stage_out2,
-                       &ctx->df_grp, &ctx->df_heads, &ctx->df_ent, &ctx->df_eseq, &ctx->df_nent, &ctx->df_usize, &ctx->df_nseq, &ctx->df_tkbase, &ctx->df_tk }) b->release();
+                       &ctx->dict_stage, &ctx->df_grp, &ctx->df_heads, &ctx->df_ent, &ctx->df_eseq, &ctx->df_nent, &ctx->df_usize, &ctx->df_nseq, &ctx->df_tkbase, &ctx->df_tk }) b->release();
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
@@ -262,6 +277,15 @@ size_t b2lz4_set_devices(b2lz4_ctx* ctx, const int* devices, int n) {
     return 0;
 }
 
+size_t b2lz4_set_dict(b2lz4_ctx* ctx, const void* dict, size_t n, uint32_t dict_id) {
+    if (!ctx || (n && !dict)) return err_code(E_GENERIC);
+    const size_t keep = std::min(n, HIST_MAX);                      // only the last 64 KB can ever be referenced (lz4frame.c:505-509)
+    ctx->dict.assign((const uint8_t*)dict + (n - keep), (const uint8_t*)dict + n);
+    ctx->dict_id = dict_id;
+    for (int k = 0; k < ctx->n_lanes; ++k) if (ctx->lanes[k]) { ctx->lanes[k]->dict = ctx->dict; ctx->lanes[k]->dict_id = dict_id; }
+    return 0;
+}
+
 size_t b2lz4_last_stats(const b2lz4_ctx* ctx, b2lz4_stats* out) {
     if (!ctx || !out) return err_code(E_GENERIC);
     *out = ctx->stats;
@@ -280,13 +304,16 @@ void b2lz4_pinned_free(void* p) { if (p) cudaFreeHost(p); }
 // runs on ctx->st2 over the input, concurrently, and its digest is stored once layout knows the offset.
 enum : unsigned { CL_WHOLE_FRAME = 1u, CL_SUM_RESET = 2u, CL_SUM_UPDATE = 4u, CL_INDEX_FRAGMENT = 8u };
 static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, uint8_t* d_dst, size_t cap,
-                              unsigned flags)
+                              unsigned flags, uint32_t hist = 0)
 {
     const bool whole_frame = (flags & CL_WHOLE_FRAME) != 0;
     const b2lz4_prefs& pr = ctx->prefs;
     EncParams P{};
     P.n = n;
     fill_desc(pr, P.desc, n);
+    if (ctx->dict_id) { P.desc.has_dict_id = 1; P.desc.dict_id = ctx->dict_id; }
+    P.linked = pr.block_linked ? 1u : 0u;
+    P.hist = P.linked ? hist : 0u;
     P.block_size = block_size_of(P.desc.block_size_id);
     const uint32_t dom = sub_size_of(pr, P.block_size);             // match domain = what one decoder warp decodes
     P.sub_size = std::min<uint32_t>(dom, ENC_UNIT);                 // encoder unit
@@ -303,7 +330,7 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
     P.block_checksum = P.desc.block_checksum;
     P.content_checksum = whole_frame ? P.desc.content_checksum : 0u;
     P.write_header = whole_frame ? 1u : 0u;
-    P.write_index = (whole_frame && pr.write_index) ? 1u : 0u;
+    P.write_index = (whole_frame && pr.write_index && !P.linked) ? 1u : 0u;   // a linked frame has no independent entry points
 
     CU(ctx->scratch.ensure((size_t)P.n_subs * P.scratch_stride));
     CU(ctx->subs.ensure((size_t)P.n_subs * sizeof(SubOut)));
@@ -378,7 +405,18 @@ size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* 
     if (!ctx || (!d_src && n) || !d_dst) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
     ctx->stats = b2lz4_stats{};
-    r = compress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, CL_WHOLE_FRAME | CL_SUM_RESET | CL_SUM_UPDATE);
+    uint32_t hist = 0;
+    if (ctx->prefs.block_linked && !ctx->dict.empty() && n) {
+        // the dictionary has to lie in front of the stream: dictionary + stream into a staging buffer (dictionary frames are
+        // small-message territory; a device-to-device copy is the simple way)
+        hist = (uint32_t)ctx->dict.size();
+        CU(ctx->dict_stage.ensure(HIST_MAX + n + 16));
+        uint8_t* st = (uint8_t*)ctx->dict_stage.p;
+        CU(cudaMemcpyAsync(st + HIST_MAX - hist, ctx->dict.data(), hist, cudaMemcpyHostToDevice, ctx->st));
+        CU(cudaMemcpyAsync(st + HIST_MAX, d_src, n, cudaMemcpyDeviceToDevice, ctx->st));
+        d_src = st + HIST_MAX;
+    }
+    r = compress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, CL_WHOLE_FRAME | CL_SUM_RESET | CL_SUM_UPDATE, hist);
     if (r) return r;
     return compress_finish(ctx, n);
 }
@@ -485,7 +523,9 @@ static uint32_t tables_for(size_t n, size_t cap) {
 // frame that asks for them
 static void df_presize(b2lz4_ctx* ctx, size_t n, size_t cap) {
     if (!df_enabled()) return;
-    if (ctx->prefs.use_index && !ctx->df_groups) return;
+    // the chain tables take 8 bytes per compressed byte: they are only allocated once a frame has asked for them (the scan
+    // reports its needs through ERROR_allocation_failed and the call is repeated), and then kept for the frames that follow
+    if (!ctx->df_groups) return;
     const uint64_t g = n / DF_G + tables_for(n, cap) + 16, t = n / (3u * DF_BATCH) + 2ull * tables_for(n, cap) + 16;
     if (g > ctx->df_groups) ctx->df_groups = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, g + g / 8);
     if (t > ctx->df_ntickets) ctx->df_ntickets = (uint32_t)std::min<uint64_t>(0x7FFFFFFFull, t + t / 8);
@@ -498,6 +538,19 @@ static size_t decompress_begin(b2lz4_ctx* ctx, const void* d_src, size_t n, void
     return decompress_launch(ctx, (const uint8_t*)d_src, n, (uint8_t*)d_dst, cap, mode, tables_for(n, cap), hist);
 }
 size_t b2lz4_decompress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed) {
+    if (ctx && !ctx->dict.empty() && d_dst && cap) {
+        // the dictionary has to lie in front of the output: decode into a staging buffer behind it, then copy
+        size_t r = set_device(ctx); if (r) return r;
+        const uint32_t hist = (uint32_t)ctx->dict.size();
+        CU(ctx->dict_stage.ensure(HIST_MAX + cap + 16));
+        uint8_t* st = (uint8_t*)ctx->dict_stage.p + HIST_MAX;
+        CU(cudaMemcpyAsync(st - hist, ctx->dict.data(), hist, cudaMemcpyHostToDevice, ctx->st));
+        r = decompress_device_impl(ctx, d_src, n, st, cap, consumed, hist);
+        if (b2lz4_is_error(r)) return r;
+        if (r) CU(cudaMemcpyAsync(d_dst, st, r, cudaMemcpyDeviceToDevice, ctx->st));
+        CU(cudaStreamSynchronize(ctx->st));
+        return r;
+    }
     return decompress_device_impl(ctx, d_src, n, d_dst, cap, consumed, 0u);
 }
 static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap, size_t* consumed,
@@ -542,7 +595,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
             // stream) or an error may stem from it: redo with the exact layout — the dataflow path computes every block's
             // decoded size before it copies a byte (without it: the blocks chained in order by one warp)
             mode = (mode & ~SCAN_USE_INDEX) | (df_enabled() ? (SCAN_DF | SCAN_DF_ALL) : SCAN_SINGLE_CHAIN);
-            if (df_enabled() && !ctx->df_groups) { const uint32_t keep = ctx->prefs.use_index; ctx->prefs.use_index = 0; df_presize(ctx, n, cap); ctx->prefs.use_index = keep; }
+
             ++ctx->stats.retries; continue;
         }
         float a = 0, b = 0, c = 0;
@@ -659,9 +712,14 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     const int L = (int)std::min<size_t>((size_t)pipe_lanes(ctx), std::max<size_t>(1, nchunks));
     r = ensure_lanes(ctx, L); if (r) return r;
     uint8_t* out = (uint8_t*)dst;
-    size_t o = whole ? b2lz4_frame_header_write(out, cap, &pr, n) : 0;
+    if (pr.block_linked) pr.write_index = 0;
+    size_t o = whole ? b2lz4_frame_header_write2(out, cap, &pr, n, ctx->dict_id) : 0;
     if (b2lz4_is_error(o)) return o;
     const bool sum = pr.content_checksum != 0, want_index = pr.write_index != 0;
+    const bool linked = pr.block_linked != 0;
+    // linked blocks: every chunk goes to its lane with the 64 KB of the stream in front of it (the input is all here, in host
+    // memory); in front of the first chunk lies the dictionary (first batch of a frame) or the tail of the batches before
+    const std::vector<uint8_t>& front = (hmode == HOSTC_BLOCKS) ? ctx->tail : ctx->dict;
     SumChain sc{ctx};
     if (sum && hmode != HOSTC_BLOCKS) sc.reset();
     std::vector<uint8_t> ix_blocks, ix_chains;             // index entries gathered from the chunks
@@ -687,18 +745,32 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
         b2lz4_ctx* ln = ctx->lanes[i % L];
         const size_t off = plan[i] * bs, len = std::min(plan[i + 1] * bs, n) - off;
         LANE_CU(ln, cudaSetDevice(ln->device));
-        LANE_CU(ln, ln->stage_in.ensure(len + 16));
+        const size_t pad = linked ? HIST_MAX : 0;
+        LANE_CU(ln, ln->stage_in.ensure(pad + len + 16));
         LANE_CU(ln, ln->stage_out.ensure(b2lz4_compress_bound(len, &pr) + 16));
         if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // the checksum pass of the lane's previous chunk
-        LANE_CU(ln, cudaMemcpyAsync(ln->stage_in.p, (const uint8_t*)src + off, len, cudaMemcpyHostToDevice, ln->st));
+        uint8_t* din = (uint8_t*)ln->stage_in.p + pad;
+        uint32_t hist = 0;
+        if (linked) {
+            const size_t own = std::min(off, HIST_MAX);                           // bytes of THIS call's input in front of the chunk
+            hist = (uint32_t)own;
+            if (own < HIST_MAX && !front.empty()) {                               // ... and, in front of those, the dictionary / earlier batches
+                const size_t more = std::min(front.size(), HIST_MAX - own);
+                LANE_CU(ln, cudaMemcpyAsync(din - own - more, front.data() + (front.size() - more), more, cudaMemcpyHostToDevice, ln->st));
+                hist += (uint32_t)more;
+            }
+            LANE_CU(ln, cudaMemcpyAsync(din - own, (const uint8_t*)src + off - own, own + len, cudaMemcpyHostToDevice, ln->st));
+        } else
+        LANE_CU(ln, cudaMemcpyAsync(din, (const uint8_t*)src + off, len, cudaMemcpyHostToDevice, ln->st));
         if (sum) {                                                              // serial XXH32 in chunk order
             LANE_CU(ln, cudaEventRecord(ln->ev_in, ln->st));
-            LANE_CU(ln, sc.update(ln, (const uint8_t*)ln->stage_in.p, len, ln->ev_in));
+            LANE_CU(ln, sc.update(ln, din, len, ln->ev_in));
             LANE_CU(ln, cudaSetDevice(ln->device));
         }
         ln->stats = b2lz4_stats{};
-        size_t e = compress_launch(ln, (const uint8_t*)ln->stage_in.p, len, (uint8_t*)ln->stage_out.p, ln->stage_out.cap,
-                                   want_index ? CL_INDEX_FRAGMENT : 0u);
+        ln->dict_id = ctx->dict_id;
+        size_t e = compress_launch(ln, din, len, (uint8_t*)ln->stage_out.p, ln->stage_out.cap,
+                                   want_index ? CL_INDEX_FRAGMENT : 0u, hist);
         if (e) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s", ln->cuda_err); return e; }
         return 0;
     };
@@ -732,6 +804,13 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     launches += sc.launches;
     if (sum && multi_dev(ctx)) for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st2));
     CU(cudaSetDevice(ctx->device));
+    if (!whole && linked) {                                                     // what the next batch's first blocks may reach back into
+        std::vector<uint8_t> t;
+        const size_t own = std::min(n, HIST_MAX);
+        if (own < HIST_MAX && !front.empty()) { const size_t more = std::min(front.size(), HIST_MAX - own); t.assign(front.end() - (long)more, front.end()); }
+        t.insert(t.end(), (const uint8_t*)src + (n - own), (const uint8_t*)src + n);
+        ctx->tail.swap(t);
+    }
     if (!whole) {
         if (sum) CU(cudaStreamSynchronize(ctx->st2));
         ctx->stats.n_blocks = blocks_total; ctx->stats.n_chains = chains_total; ctx->stats.kernel_launches = launches;
@@ -778,15 +857,19 @@ static size_t decompress_host_whole(b2lz4_ctx* ctx, const void* src, size_t n, v
     if (!ctx || !src || (!dst && cap)) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
     CU(ctx->stage_in.ensure(n + 16));
-    CU(ctx->stage_out.ensure(cap + 16));
+    CU(ctx->stage_out.ensure(HIST_MAX + cap + 16));
     cudaEvent_t e0 = ctx->ev[4], e1 = ctx->ev[5], e2 = ctx->ev[6], e3 = ctx->ev[7];
     CU(cudaEventRecord(e0, ctx->st));
     CU(cudaMemcpyAsync(ctx->stage_in.p, src, n, cudaMemcpyHostToDevice, ctx->st));
+    // a dictionary (LZ4F_decompress_usingDict, lz4frame.c:1842-1860) is history in front of the first block (linked frames)
+    uint8_t* dout = (uint8_t*)ctx->stage_out.p + HIST_MAX;
+    const uint32_t hist = (uint32_t)ctx->dict.size();
+    if (hist) CU(cudaMemcpyAsync(dout - hist, ctx->dict.data(), hist, cudaMemcpyHostToDevice, ctx->st));
     CU(cudaEventRecord(e1, ctx->st));
-    r = b2lz4_decompress_device(ctx, ctx->stage_in.p, n, ctx->stage_out.p, cap, consumed);
+    r = decompress_device_impl(ctx, ctx->stage_in.p, n, dout, cap, consumed, hist);
     if (b2lz4_is_error(r)) return r;
     CU(cudaEventRecord(e2, ctx->st));
-    if (r) CU(cudaMemcpyAsync(dst, ctx->stage_out.p, r, cudaMemcpyDeviceToHost, ctx->st));
+    if (r) CU(cudaMemcpyAsync(dst, dout, r, cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaEventRecord(e3, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
     cudaEventElapsedTime(&ctx->stats.ms_h2d, e0, e1);
@@ -1114,6 +1197,10 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     const bool linked = !legacy && !info->block_independent;
     if (linked) {
         r = ring_reserve(ctx, cap); if (r) return r;
+        if ((flags & B2LZ4_STREAM_FIRST) && !ctx->dict.empty()) {      // the dictionary is the frame's first history (lz4frame.c:1842-1860)
+            ctx->ring_hist = (uint32_t)ctx->dict.size();
+            CU(cudaMemcpyAsync((uint8_t*)ctx->ring.p + ctx->ring_pos - ctx->ring_hist, ctx->dict.data(), ctx->ring_hist, cudaMemcpyHostToDevice, ctx->st));
+        }
         dout = (uint8_t*)ctx->ring.p + ctx->ring_pos; hist = ctx->ring_hist;
     } else {
         CU(ctx->stage_out.ensure(cap + 16));

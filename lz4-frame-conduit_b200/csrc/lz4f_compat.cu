@@ -15,6 +15,7 @@
 #include <chrono>
 #include <future>
 #include <mutex>
+#include <vector>
 #include <stdio.h>
 #include "format.h"
 #include "../../include/b200lz4.h"
@@ -177,7 +178,42 @@ size_t LZ4F_compressBound(size_t srcSize, const LZ4F_preferences_t* p) {
     return blocks_bound(buffered + srcSize, bs, p->frameInfo.blockChecksumFlag != 0) + 8;
 }
 
+}  // extern "C"
+
+struct LZ4F_CDict_s { std::vector<uint8_t> bytes; };
+
+// LZ4F_blockLinked is the ZERO value of blockMode, i.e. what every caller that never thought about it passes (the reference
+// conduit included, Conduit.hsc:248-263).  Frames with independent blocks are what this codec decodes in parallel, and any
+// decoder accepts them, so plain LZ4F_compressBegin writes independent blocks unless B2LZ4_BLOCK_MODE=honour asks for the
+// field to be taken literally; LZ4F_compressBegin_usingCDict always takes it literally (a dictionary is only used by linked
+// blocks here, and a caller that brings one wants it used).
+static bool honour_block_mode() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_BLOCK_MODE"); v = (e && (*e == 'h' || *e == 'l')) ? 1 : 0; } return v == 1; }
+
+static size_t begin_impl(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_preferences_t* p, const LZ4F_CDict_s* cdict, bool literal_mode);
+
+extern "C" {
+
 size_t LZ4F_compressBegin(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_preferences_t* p) {
+    return begin_impl(c, dst, cap, p, nullptr, honour_block_mode());
+}
+
+LZ4F_CDict* LZ4F_createCDict(const void* dictBuffer, size_t dictSize) {            // lz4frame.c:478-512: keeps the last 64 KB
+    if (!dictBuffer && dictSize) return nullptr;
+    LZ4F_CDict_s* d = new (std::nothrow) LZ4F_CDict_s();
+    if (!d) return nullptr;
+    const size_t keep = std::min<size_t>(dictSize, 65536);
+    d->bytes.assign((const uint8_t*)dictBuffer + (dictSize - keep), (const uint8_t*)dictBuffer + dictSize);
+    return d;
+}
+void LZ4F_freeCDict(LZ4F_CDict* d) { delete d; }                                   // lz4frame.c:514-521
+
+size_t LZ4F_compressBegin_usingCDict(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_CDict* cdict, const LZ4F_preferences_t* p) {
+    return begin_impl(c, dst, cap, p, cdict, true);
+}
+
+}  // extern "C"
+
+static size_t begin_impl(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_preferences_t* p, const LZ4F_CDict_s* cdict, bool literal_mode) {
     if (!c || !dst) return ec(E_GENERIC);
     if (cap < (size_t)LZ4F_HEADER_SIZE_MAX) return ec(E_dstMaxSize_tooSmall);       // lz4frame.c:613
     drop_flight(c);                                                              // a frame abandoned without compressEnd
@@ -192,6 +228,7 @@ size_t LZ4F_compressBegin(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_prefer
     c->bp.content_checksum = c->prefs.frameInfo.contentChecksumFlag != 0;
     c->bp.content_size = c->prefs.frameInfo.contentSize != 0;
     c->bp.write_index = 0;
+    c->bp.block_linked = (literal_mode && c->prefs.frameInfo.blockMode == LZ4F_blockLinked) ? 1u : 0u;
     c->block_size = block_bytes_of(id);
     c->batch = batch_bytes();
     if (!c->gpu) {
@@ -204,9 +241,14 @@ size_t LZ4F_compressBegin(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_prefer
         if (b2lz4_is_error(r)) return r;
     }
     c->in_len = 0; c->total_in = 0; c->first = true; c->begun = true;
-    // frames always carry independent blocks; a dictID in the preferences is not supported (no dictionary is applied)
-    return b2lz4_frame_header_write(dst, cap, &c->bp, c->prefs.frameInfo.contentSize);
+    // the dictionary (used by linked blocks only) and the dictID of the preferences (written as given, lz4frame.c:692-695)
+    const bool use_dict = cdict && c->bp.block_linked && !cdict->bytes.empty();
+    size_t r = b2lz4_set_dict(c->gpu, use_dict ? cdict->bytes.data() : nullptr, use_dict ? cdict->bytes.size() : 0, c->prefs.frameInfo.dictID);
+    if (b2lz4_is_error(r)) return r;
+    return b2lz4_frame_header_write2(dst, cap, &c->bp, c->prefs.frameInfo.contentSize, c->prefs.frameInfo.dictID);
 }
+
+extern "C" {
 
 // compresses the staged bytes [0, n) into dst; returns bytes written
 // the batch in flight has to finish; its blocks go to dst.  Returns bytes written.
@@ -351,6 +393,7 @@ struct LZ4F_dctx_s {
     bool first = true;
     size_t pre_acked = 0;                                    // input bytes already buffered but reported as unconsumed
     size_t batch = 0;
+    std::vector<uint8_t> dict;                               // LZ4F_decompress_usingDict: last 64 KB of the dictionary of the current frame
     Trace tr;
 };
 
@@ -361,6 +404,7 @@ void dctx_reset(LZ4F_dctx_s* d) {
     d->stage = DS_HEADER; d->hdr_len = 0; d->in_len = 0; d->complete_end = 0; d->n_complete = 0; d->need = 0;
     d->skip_left = 0; d->out_len = d->out_pos = 0; d->total_out = 0; d->first = true; d->pre_acked = 0;
     d->check_sum = false; d->stored_sum = 0;
+    d->dict.clear();                                             // a dictionary belongs to one frame (LZ4F_decompress_usingDict registers it again)
 }
 
 bool job_done(LZ4F_dctx_s* d) { return d->job.wait_for(std::chrono::seconds(0)) == std::future_status::ready; }
@@ -399,6 +443,10 @@ size_t decode_batch(LZ4F_dctx_s* d) {
     if (!d->in2.ensure(std::max(tail + 8, d->in.cap / 2))) return ec(E_allocation_failed);
     memcpy(d->in2.p, d->in.p + d->complete_end, tail);
     std::swap(d->in, d->in2);
+    if (d->first) {                                          // (also clears the dictionary of an earlier frame)
+        r = b2lz4_set_dict(d->gpu, d->dict.empty() ? nullptr : d->dict.data(), d->dict.size(), 0);
+        if (b2lz4_is_error(r)) return r;
+    }
     b2lz4_ctx* gpu = d->gpu; const b2lz4_frame_info info = d->info;
     const uint8_t* src = d->in2.p; const size_t n = d->complete_end; uint8_t* dst = d->out2.p;
     const unsigned flags = d->first ? B2LZ4_STREAM_FIRST : 0u;
@@ -415,9 +463,10 @@ size_t header_done(LZ4F_dctx_s* d) {
     size_t r = b2lz4_frame_header_parse(d->hdr, d->hdr_len, &d->info);
     if (b2lz4_is_error(r)) return r;
     d->stage = DS_BLOCK_HEADER; d->hdr_len = 0; d->need = 4;
-    // a foreign block is decoded by ONE warp (no side information to start inside it), at ~0.1 GB/s: what makes a batch
-    // fast is the number of blocks in it, so batches of large blocks are sized by count (64 blocks, at most 256 MiB)
-    d->batch = std::max(batch_bytes(), std::min<size_t>((size_t)64 * d->info.block_size, (size_t)256 << 20));
+    // a large foreign block is one unit of the dataflow decoder (one CTA, ~0.5 GB/s on log-like data): what makes a batch
+    // fast is the number of blocks in it, so batches of large blocks are sized by count (16 blocks = 64 MiB of 4 MB blocks;
+    // more would cost more in pinned staging than it gains)
+    d->batch = std::max(batch_bytes(), std::min<size_t>((size_t)16 * d->info.block_size, (size_t)64 << 20));
     if (getenv("B2LZ4_BATCH_MB")) d->batch = batch_bytes();
     return 0;
 }
@@ -482,6 +531,17 @@ size_t LZ4F_getFrameInfo(LZ4F_dctx* d, LZ4F_frameInfo_t* fi, const void* src, si
     if (b2lz4_is_error(r)) { d->hdr_len = 0; return r; }
     *srcSizePtr = hs; fill();
     return 4;                                                                        // next: a block header
+}
+
+// lz4frame.c:1842-1860: the dictionary is registered when the frame starts; it is copied (the reference uses it in place)
+size_t LZ4F_decompress_usingDict(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const void* srcBuffer, size_t* srcSizePtr,
+                                 const void* dict, size_t dictSize, const LZ4F_decompressOptions_t* opt) {
+    if (!d) return ec(E_GENERIC);
+    if (d->stage == DS_HEADER && d->hdr_len == 0 && d->first) {
+        const size_t keep = std::min<size_t>(dict ? dictSize : 0, 65536);
+        if (keep) d->dict.assign((const uint8_t*)dict + (dictSize - keep), (const uint8_t*)dict + dictSize); else d->dict.clear();
+    }
+    return LZ4F_decompress(d, dstBuffer, dstSizePtr, srcBuffer, srcSizePtr, opt);
 }
 
 size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const void* srcBuffer, size_t* srcSizePtr,

@@ -16,10 +16,13 @@
  * All functions return the number of bytes produced, or an LZ4F error code (test with
  * LZ4F_isError), or REPLAY_ERR_* for harness-level failures that the Haskell code reports with
  * throwString.
+ *   ref_frame_compress_dict / ref_frame_decompress_dict   the dictionary entry points (LZ4F_createCDict,
+ *                           LZ4F_compressBegin_usingCDict, LZ4F_decompress_usingDict; lz4frame.h:530-607)
  */
 #include <stdlib.h>
 #include <string.h>
 #include <stdint.h>
+#define LZ4F_STATIC_LINKING_ONLY          /* the reference declares the dictionary API in its static-linking section */
 #include "lz4frame.h"
 /* -DREPLAY_AGAINST_B200: the same replay compiled against include/lz4frame.h and linked to libb200lz4.so —
  * tests/ use it to drive the product's LZ4F_* layer with exactly the calls the Haskell conduit makes. */
@@ -277,3 +280,65 @@ unsigned ref_xxh32_stream(const void* p_, size_t n, unsigned seed, size_t piece)
 
 size_t ref_sizeof_frameinfo(void)   { return sizeof(LZ4F_frameInfo_t); }
 size_t ref_sizeof_preferences(void) { return sizeof(LZ4F_preferences_t); }
+
+
+/* Streaming compression with a dictionary: LZ4F_createCDict + LZ4F_compressBegin_usingCDict (lz4frame.c:478-521, 594-702),
+ * then LZ4F_compressUpdate per `updateChunk` bytes and LZ4F_compressEnd (what lz4/tests/frametest.c:520-662 exercises). */
+size_t ref_frame_compress_dict(const void* src_, size_t n, void* dst_, size_t cap, const void* dict, size_t dictSize,
+                               int blockSizeID, int blockIndependent, int contentChecksum, unsigned dictID, size_t updateChunk)
+{
+    const uint8_t* src = (const uint8_t*)src_;
+    uint8_t* dst = (uint8_t*)dst_;
+    LZ4F_cctx* ctx = NULL;
+    LZ4F_CDict* cd = LZ4F_createCDict(dict, dictSize);
+    if (!cd) return REPLAY_ERR_ALLOC;
+    LZ4F_preferences_t prefs; memset(&prefs, 0, sizeof prefs);
+    prefs.frameInfo.blockSizeID = (LZ4F_blockSizeID_t)blockSizeID;
+    prefs.frameInfo.blockMode = blockIndependent ? LZ4F_blockIndependent : LZ4F_blockLinked;
+    prefs.frameInfo.contentChecksumFlag = contentChecksum ? LZ4F_contentChecksumEnabled : LZ4F_noContentChecksum;
+    prefs.frameInfo.dictID = dictID;
+    size_t r = LZ4F_createCompressionContext(&ctx, LZ4F_VERSION);
+    if (LZ4F_isError(r)) { LZ4F_freeCDict(cd); return r; }
+    size_t o = 0;
+    r = LZ4F_compressBegin_usingCDict(ctx, dst, cap, cd, &prefs);
+    if (LZ4F_isError(r)) goto done;
+    o += r;
+    if (updateChunk == 0) updateChunk = n ? n : 1;
+    for (size_t pos = 0; pos < n; ) {
+        size_t piece = MINSZ(updateChunk, n - pos);
+        r = LZ4F_compressUpdate(ctx, dst + o, cap - o, src + pos, piece, NULL);
+        if (LZ4F_isError(r)) goto done;
+        o += r; pos += piece;
+    }
+    r = LZ4F_compressEnd(ctx, dst + o, cap - o, NULL);
+    if (LZ4F_isError(r)) goto done;
+    o += r; r = o;
+done:
+    LZ4F_freeCompressionContext(ctx);
+    LZ4F_freeCDict(cd);
+    return r;
+}
+
+/* LZ4F_decompress_usingDict (lz4frame.c:1842-1860) in a loop over `chunk`-byte input slices. */
+size_t ref_frame_decompress_dict(const void* src_, size_t n, void* dst_, size_t cap, const void* dict, size_t dictSize, size_t chunk)
+{
+    const uint8_t* src = (const uint8_t*)src_;
+    uint8_t* dst = (uint8_t*)dst_;
+    LZ4F_dctx* ctx = NULL;
+    size_t r = LZ4F_createDecompressionContext(&ctx, LZ4F_VERSION);
+    if (LZ4F_isError(r)) return r;
+    size_t ip = 0, op = 0, hint = 1;
+    if (chunk == 0) chunk = n ? n : 1;
+    while (hint != 0) {
+        if (ip == n) { r = REPLAY_ERR_NO_ENDMARK; goto done; }
+        size_t ssz = MINSZ(chunk, n - ip), dsz = cap - op;
+        hint = LZ4F_decompress_usingDict(ctx, dst + op, &dsz, src + ip, &ssz, dict, dictSize, NULL);
+        if (LZ4F_isError(hint)) { r = hint; goto done; }
+        ip += ssz; op += dsz;
+        if (ssz == 0 && dsz == 0 && op == cap) { r = REPLAY_ERR_DST_TOO_SMALL; goto done; }
+    }
+    r = op;
+done:
+    LZ4F_freeDecompressionContext(ctx);
+    return r;
+}

@@ -114,6 +114,11 @@ def ref():
     lib.LZ4_compress_default.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
     lib.LZ4_decompress_safe.restype = C.c_int
     lib.LZ4_decompress_safe.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
+    if hasattr(lib, "ref_frame_compress_dict"):
+        lib.ref_frame_compress_dict.restype = sz
+        lib.ref_frame_compress_dict.argtypes = [C.c_char_p, sz, C.c_char_p, sz, C.c_char_p, sz, C.c_int, C.c_int, C.c_int, C.c_uint, sz]
+        lib.ref_frame_decompress_dict.restype = sz
+        lib.ref_frame_decompress_dict.argtypes = [C.c_char_p, sz, C.c_char_p, sz, C.c_char_p, sz, sz]
     return lib
 
 
@@ -130,7 +135,29 @@ def _bind_replay(lib):
     lib.ref_frame_compress.argtypes = [C.c_char_p, sz, C.c_char_p, sz] + [C.c_int] * 6 + [sz]
     lib.ref_sizeof_frameinfo.restype = sz
     lib.ref_sizeof_preferences.restype = sz
+    lib.ref_frame_compress_dict.restype = sz
+    lib.ref_frame_compress_dict.argtypes = [C.c_char_p, sz, C.c_char_p, sz, C.c_char_p, sz, C.c_int, C.c_int, C.c_int, C.c_uint, sz]
+    lib.ref_frame_decompress_dict.restype = sz
+    lib.ref_frame_decompress_dict.argtypes = [C.c_char_p, sz, C.c_char_p, sz, C.c_char_p, sz, sz]
     return lib
+
+
+def dict_compress(lib, data, dic, bsid=4, indep=0, cc=1, dict_id=0, chunk=16384):
+    """LZ4F_createCDict + LZ4F_compressBegin_usingCDict + updates + end (oracle/conduit_replay.c) on `lib`'s LZ4F_* symbols."""
+    cap = len(data) + len(data) // 50 + 70000
+    out = C.create_string_buffer(cap)
+    r = lib.ref_frame_compress_dict(data, len(data), out, cap, dic, len(dic), bsid, indep, cc, dict_id, chunk)
+    assert r < (1 << 62), f"dict compress failed with code {(1 << 64) - r}"
+    return out.raw[:r]
+
+
+def dict_decompress(lib, frame, dic, cap, chunk=0):
+    """LZ4F_decompress_usingDict in a loop; returns the bytes or a negative error number."""
+    out = C.create_string_buffer(cap + 1)
+    r = lib.ref_frame_decompress_dict(frame, len(frame), out, cap, dic, len(dic), chunk)
+    if r > (1 << 62):
+        return -((1 << 64) - r)
+    return out.raw[:r]
 
 
 def build_replay_b200():

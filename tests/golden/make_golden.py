@@ -23,6 +23,8 @@ ref.ref_frame_compress.restype = sz
 ref.ref_frame_compress.argtypes = [C.c_char_p, sz, C.c_char_p, sz] + [C.c_int] * 6 + [sz]
 ref.ref_xxh32.restype = C.c_uint
 ref.ref_xxh32.argtypes = [C.c_char_p, sz, C.c_uint]
+ref.ref_frame_compress_dict.restype = sz
+ref.ref_frame_compress_dict.argtypes = [C.c_char_p, sz, C.c_char_p, sz, C.c_char_p, sz, C.c_int, C.c_int, C.c_int, C.c_uint, sz]
 
 
 def payloads():
@@ -100,6 +102,23 @@ def main():
             ent["frames"][kind] = {"file": fn, "size": len(fr), "xxh32": ref.ref_xxh32(fr, len(fr), 0),
                                    "head": fr[:7].hex()}
         man[name] = ent
+    # ---- dictionary frames (LZ4F_compressBegin_usingCDict, lz4frame.c:594-702; lz4/tests/frametest.c:520-662): linked blocks,
+    # the dictionary = 40 KB of the reference's generator with another seed; with and without a dictID in the header
+    dic = subprocess.run([os.path.join(REF, "datagen"), "-g40000", "-s1"], capture_output=True, check=True).stdout[:40000]
+    with open(os.path.join(HERE, "dict40k.raw"), "wb") as f:
+        f.write(dic)
+    dman = {"file": "dict40k.raw", "size": len(dic), "frames": {}}
+    for name, did in (("hello", 0), ("numbers", 0x00C0FFEE), ("datagen200k", 0), ("mixed166k", 7)):
+        data = ps[name]
+        cap = len(data) + len(data) // 50 + 70000
+        out = C.create_string_buffer(cap)
+        r = ref.ref_frame_compress_dict(data, len(data), out, cap, dic, len(dic), 4, 0, 1, did, 16384)
+        assert r < (1 << 62), r
+        fn = f"{name}.lib_dict.lz4"
+        with open(os.path.join(HERE, fn), "wb") as f:
+            f.write(out.raw[:r])
+        dman["frames"][name] = {"file": fn, "size": r, "dict_id": did, "head": out.raw[:11].hex()}
+    man["_dict"] = dman
     man["_xxh32_kat"] = {"": ref.ref_xxh32(b"", 0, 0), "abc": ref.ref_xxh32(b"abc", 3, 0),
                          "hello*4": ref.ref_xxh32(b"hellohellohellohello", 20, 0)}
     with open(os.path.join(HERE, "manifest.json"), "w") as f:

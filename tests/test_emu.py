@@ -13,7 +13,7 @@ import sys
 
 import pytest
 
-from conftest import ROOT, gen_bytes, golden_bytes, orc_decode, ref_conduit_decode, _bind_replay
+from conftest import ROOT, gen_bytes, golden_bytes, orc_decode, ref_conduit_decode, _bind_replay, dict_compress, dict_decompress
 
 EMU_LIB = os.path.join(ROOT, "tests", "_build", "libb200lz4_emu.so")
 sz = C.c_size_t
@@ -70,7 +70,7 @@ def test_emu_decodes_every_golden_frame(emu, manifest):
                 f = golden_bytes(fr["file"])
                 out, used = c.decompress_bytes(f)
                 assert out == raw and used == len(f), (name, kind)
-                if name in ("datagen200k", "mixed166k"):        # several KB of tokens per block: more pieces than blocks
+                if name in ("datagen200k", "mixed166k") and kind in ("conduit", "cli_B4_BD"):   # linked: dataflow tickets
                     assert c.stats().n_chains > c.stats().n_blocks, (name, kind, "not decoded by pieces")
                 n += 1
     assert n >= 35
@@ -150,6 +150,61 @@ def test_emu_reference_made_linked_frame(emu, emu_replay, ref, gen):
     assert got == d and used == len(frame)
 
 
+def test_emu_linked_block_encoding(emu, oracle, ref, lz4_cli, datagen, gen):
+    """blockMode = linked: FLG 0x40 frames whose matches cross block borders.  Every decoder takes them, and
+    at 64 KB blocks the size is within the 2 % of the reference's default (linked 64 KB) that independent blocks cannot reach."""
+    shapes = [gen_bytes(gen, "loglike", 500000), bytes(200000) + gen_bytes(gen, "random", 70000, 2) + gen_bytes(gen, "textlike", 90000, 4), b"ab" * 7]
+    if datagen:
+        shapes.append(subprocess.run([datagen, "-g1500000", "-s1"], capture_output=True, check=True).stdout)
+    with emu.Codec(0, use_index=0) as c:
+        for bid in (4, 5):
+            c.set_prefs(block_size_id=bid, sub_block_log2=16 if bid == 4 else 18, block_linked=1, write_index=0, content_checksum=1)
+            for d in shapes:
+                fr = c.compress_bytes(d)
+                assert fr[4] & 0x20 == 0                                  # FLG bit 5 clear: linked (lz4_Frame_format.md:136-138)
+                got, used = orc_decode(oracle, fr, len(d) + 16)
+                assert got == d and used == len(fr), (bid, len(d))
+                assert c.decompress_bytes(fr)[0] == d
+                if lz4_cli:
+                    assert subprocess.run([lz4_cli, "-d", "-c"], input=fr, capture_output=True).stdout == d
+                if ref is not None and len(d) > 400000:
+                    cap = len(d) + len(d) // 100 + 100000
+                    o = C.create_string_buffer(cap)
+                    r = ref.ref_conduit_compress(d, len(d), o, cap, 0, 0)
+                    assert len(fr) <= r * 1.02, (bid, len(fr), r)
+
+
+def test_emu_dictionary_frames_both_ways(emu_replay, ref, lz4_cli, manifest, gen, tmp_path):
+    """LZ4F_createCDict / LZ4F_compressBegin_usingCDict / LZ4F_decompress_usingDict (lz4frame.c:478-521, 594-702, 1842-1860):
+    reference-made dictionary frames (committed goldens) decode here; frames made here decode with the reference library
+    and with `lz4 -d -D`; without the dictionary they must not."""
+    dman = manifest["_dict"]
+    dic = golden_bytes(dman["file"])
+    for name, fr in dman["frames"].items():
+        raw = golden_bytes(manifest[name]["raw"])[:manifest[name]["size"]]
+        f = golden_bytes(fr["file"])
+        assert dict_decompress(emu_replay, f, dic, len(raw) + 64, 7000) == raw, name
+        if name in ("datagen200k", "mixed166k"):                                          # same generator as the dictionary:
+            assert dict_decompress(emu_replay, f, b"", len(raw) + 64) != raw, name       # the dictionary is really needed
+    dfile = tmp_path / "dict"
+    dfile.write_bytes(dic)
+    for d in (b"", b"x", dic[5000:5300], dic[100:9000] + gen_bytes(gen, "loglike", 100000), gen_bytes(gen, "textlike", 300000, 3)):
+        for did in (0, 0xABCD1234):
+            ours = dict_compress(emu_replay, d, dic, 4, 0, 1, did)
+            assert ours[4] & 0x20 == 0 and bool(ours[4] & 1) == bool(did)
+            assert dict_decompress(emu_replay, ours, dic, len(d) + 64, 999) == d
+            if ref is not None:
+                assert dict_decompress(ref, ours, dic, len(d) + 64, 1000) == d
+                theirs = dict_compress(ref, d, dic, 4, 0, 1, did)
+                assert ours[:len(theirs[:11]) if did else 7] == theirs[:11 if did else 7]        # same header bytes
+                assert dict_decompress(emu_replay, theirs, dic, len(d) + 64) == d
+                if 200 < len(d) < 10000:
+                    assert len(ours) < len(dict_compress(emu_replay, d, b"", 4, 0, 1, did))   # the dictionary pays
+            if lz4_cli:
+                r = subprocess.run([lz4_cli, "-d", "-c", "-D", str(dfile)], input=ours, capture_output=True)
+                assert r.returncode == 0 and r.stdout == d
+
+
 def _run_with_env(env, code):
     e = dict(os.environ); e.update(env); e["B2LZ4_LIB"] = EMU_LIB
     p = subprocess.run([sys.executable, "-c", code], env=e, capture_output=True, text=True, timeout=600, cwd=ROOT)
@@ -173,6 +228,12 @@ with pkg.Codec(0, use_index=0) as c:
         assert c.decompress_bytes(fr)[0] == raw
 print('ok')
 """
+
+
+def test_emu_dataflow_forced_for_every_frame(emu):
+    """B2LZ4_DF=2: independent small-block frames (normally one warp per block) through the dataflow kernels as well."""
+    assert "ok" in _run_with_env({"B2LZ4_DF": "2"}, _GOLDEN_LOOP)
+    assert "ok" in _run_with_env({"B2LZ4_DF": "0"}, _GOLDEN_LOOP)          # and everything without them
 
 
 def test_emu_lane_order_does_not_matter(emu):

@@ -118,6 +118,25 @@ def test_cli_legacy_low_ratio_blocks_over_4mib(lz4_cli):
     assert run([CLI, "-d", "--all-frames"], frame).stdout == data
 
 
+def test_cli_linked_blocks_and_dictionary(lz4_cli, gen, tmp_path):
+    """-BD (linked blocks) and -D FILE (dictionary): interchangeable with `lz4 -BD` / `lz4 -D` in both directions."""
+    dic = gen_bytes(gen, "loglike", 50000, 5)
+    dfile = tmp_path / "d.bin"; dfile.write_bytes(dic)
+    data = dic[1000:4000] + gen_bytes(gen, "loglike", (5 << 20) + 17, 6)
+    fr = run([CLI, "-B4", "-BD"], data).stdout
+    assert fr[4] & 0x20 == 0                                        # linked
+    assert run([lz4_cli, "-d", "-c"], fr).stdout == data and run([CLI, "-d"], fr).stdout == data
+    assert run([CLI, "-d"], run([lz4_cli, "-c", "-B4", "-BD"], data).stdout).stdout == data
+    small = dic[2000:2600]
+    for payload in (small, data):
+        ours = run([CLI, "-B4", "-D", str(dfile)], payload).stdout
+        assert run([lz4_cli, "-d", "-c", "-D", str(dfile)], ours).stdout == payload
+        assert run([CLI, "-d", "-D", str(dfile)], ours).stdout == payload
+        theirs = run([lz4_cli, "-c", "-B4", "-BD", "-D", str(dfile)], payload).stdout
+        assert run([CLI, "-d", "-D", str(dfile)], theirs).stdout == payload
+    assert len(run([CLI, "-B4", "-D", str(dfile)], small).stdout) < len(run([CLI, "-B4"], small).stdout)
+
+
 def test_cli_errors_match_the_conduit(lz4_cli):
     frame = run([lz4_cli, "-c"], b"hellohellohellohello" * 1000).stdout
     p = run([CLI, "-d"], frame[:-6], ok=False)

@@ -13,7 +13,7 @@ import subprocess
 
 import pytest
 
-from conftest import golden_bytes, orc_decode, ref_conduit_decode, gen_bytes, sz
+from conftest import golden_bytes, orc_decode, ref_conduit_decode, gen_bytes, sz, dict_compress, dict_decompress
 
 pytestmark = pytest.mark.gpu
 
@@ -148,3 +148,63 @@ def test_truncated_stream_reports_no_endmark(replay, manifest):
     assert got == -102, got                                  # REPLAY_ERR_NO_ENDMARK (the conduit's throwString)
     got, _ = ref_conduit_decode(replay, b[:3], 400000, 0)
     assert got == -101, got                                  # "not enough bytes for header" (Conduit.hsc:615-616)
+
+
+# ------------------------------------------------------------------ linked-block encoding and dictionaries
+def test_linked_block_encoding_ratio_and_interop(pkg, oracle, ref, lz4_cli, datagen, gen):
+    """blockMode = linked honoured (FLG 0x40): every decoder takes the frames; at 64 KB blocks — the reference conduit's own
+    shape, BASELINE config 1 — the size is within the 2 % of the reference's default that independent 64 KB blocks miss."""
+    assert ref is not None and datagen
+    text = subprocess.run([datagen, "-g67108864", "-s1"], capture_output=True, check=True).stdout
+    shapes = {"datagen 64 MiB": text, "log-like 32 MiB": gen_bytes(gen, "loglike", 32 << 20),
+              "mix": bytes(300000) + gen_bytes(gen, "random", 200000, 2) + gen_bytes(gen, "textlike", 900000, 4), "tiny": b"ab" * 7}
+    with pkg.Codec(0, use_index=0) as c:
+        for bid in (4, 7):
+            c.set_prefs(block_size_id=bid, sub_block_log2=16 if bid == 4 else 17, block_linked=1, write_index=0, content_checksum=1)
+            for what, d in shapes.items():
+                fr = c.compress_bytes(d)
+                assert fr[4] & 0x20 == 0
+                got, used = orc_decode(oracle, fr, len(d) + 16)
+                assert got == d and used == len(fr), (bid, what)
+                assert c.decompress_bytes(fr)[0] == d, (bid, what)
+                got, used = ref_conduit_decode(ref, fr, len(d) + 64)
+                assert got == d, (bid, what)
+                if lz4_cli and len(d) < (8 << 20):
+                    assert subprocess.run([lz4_cli, "-d", "-c"], input=fr, capture_output=True).stdout == d
+                if len(d) > (1 << 20) and what != "mix":
+                    cap = len(d) + len(d) // 100 + 100000
+                    o = C.create_string_buffer(cap)
+                    r = ref.ref_conduit_compress(d, len(d), o, cap, 0, 0)
+                    print(f"linked {65536 << (2 * (bid - 4))} B blocks, {what}: ours {len(fr)} B, reference default {r} B ({100.0 * (len(fr) / r - 1):+.2f} %)")
+                    assert len(fr) <= r * 1.02, (bid, what, len(fr), r)
+
+
+def test_dictionary_frames_both_ways(replay, ref, lz4_cli, manifest, gen, tmp_path):
+    """LZ4F_createCDict / LZ4F_compressBegin_usingCDict / LZ4F_decompress_usingDict on the product's symbols: reference-made
+    dictionary frames (goldens) decode here; frames made here decode with the reference library and `lz4 -d -D`."""
+    dman = manifest["_dict"]
+    dic = golden_bytes(dman["file"])
+    for name, fr in dman["frames"].items():
+        raw = golden_bytes(manifest[name]["raw"])[:manifest[name]["size"]]
+        f = golden_bytes(fr["file"])
+        assert dict_decompress(replay, f, dic, len(raw) + 64, 7000) == raw, name
+        if name in ("datagen200k", "mixed166k"):
+            assert dict_decompress(replay, f, b"", len(raw) + 64) != raw, name
+    dfile = tmp_path / "dict"
+    dfile.write_bytes(dic)
+    big = dic[100:30000] + gen_bytes(gen, "loglike", 20 << 20)              # several batches (B2LZ4_BATCH_MB=8)
+    for d in (b"", b"x", dic[5000:5300], dic[100:9000] + gen_bytes(gen, "loglike", 100000), gen_bytes(gen, "textlike", 300000, 3), big):
+        for did in (0, 0xABCD1234):
+            ours = dict_compress(replay, d, dic, 4, 0, 1, did)
+            assert ours[4] & 0x20 == 0 and bool(ours[4] & 1) == bool(did)
+            assert dict_decompress(replay, ours, dic, len(d) + 64, 99999) == d
+            if ref is not None:
+                assert dict_decompress(ref, ours, dic, len(d) + 64, 100000) == d
+                theirs = dict_compress(ref, d, dic, 4, 0, 1, did)
+                assert ours[:11 if did else 7] == theirs[:11 if did else 7]
+                assert dict_decompress(replay, theirs, dic, len(d) + 64) == d
+                if 200 < len(d) < 10000:
+                    assert len(ours) < len(dict_compress(replay, d, b"", 4, 0, 1, did))
+            if lz4_cli and len(d) < (1 << 20):
+                r = subprocess.run([lz4_cli, "-d", "-c", "-D", str(dfile)], input=ours, capture_output=True)
+                assert r.returncode == 0 and r.stdout == d
