@@ -81,8 +81,9 @@ void   b2lz4_default_prefs(b2lz4_prefs* prefs);
 size_t b2lz4_set_devices(b2lz4_ctx* ctx, const int* devices, int n);
 /* Dictionary (replaces LZ4F_createCDict + LZ4F_compressBegin_usingCDict / LZ4F_decompress_usingDict, lz4/lib/lz4frame.c:478-521,
  * 594-702, 1842-1860): the bytes are treated as stream history in front of the first block of every frame that follows.  Only the
- * last 64 KB matter and are kept (copied).  Linked-block frames only (prefs.block_linked on the compress side; on the decompress side
- * a match of an INDEPENDENT block that reaches into the dictionary is reported as ERROR_decompressionFailed).  dict_id != 0 is
+ * last 64 KB matter and are kept (copied).  The compressor uses it for linked-block frames (prefs.block_linked); the decompressor
+ * (host-buffer entry points) also takes independent-block frames with a dictionary, which `lz4 -D` writes for one-block inputs
+ * (lz4frame.c:392-395), one block at a time.  dict_id != 0 is
  * written into the frame header (lz4frame.c:692-695).  n = 0 removes the dictionary. */
 size_t b2lz4_set_dict(b2lz4_ctx* ctx, const void* dict, size_t n, uint32_t dict_id);
 int    b2lz4_device_count(void);

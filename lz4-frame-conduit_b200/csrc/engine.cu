@@ -14,6 +14,7 @@
 #include <new>
 #include <algorithm>
 #include <vector>
+#include <future>
 #include "kernels.h"
 #include "../../include/b200lz4.h"
 
@@ -82,13 +83,15 @@ struct b2lz4_ctx {
     // (every device reads and writes it in stream order).
     int devs[16] = {};
     int n_devs = 0;
-    XxhState* h_xxh = nullptr;
-    bool sum_host = false;                        // the running content checksum of the current frame lives in h_xxh
     uint8_t* h_frag = nullptr; size_t h_frag_cap = 0;   // pinned: index fragments of the chunks
     // dictionary (LZ4F_createCDict / LZ4F_decompress_usingDict, lz4frame.c:478-521, 1842-1860): its last 64 KB, what a
     // block can reach (lz4_Frame_format.md:226-240).  Used by linked-block frames, on both sides.
     std::vector<uint8_t> dict; uint32_t dict_id = 0;
     std::vector<uint8_t> tail;                    // linked-block streaming compression: the last 64 KB of the batches so far
+    // content checksum of host-buffer calls: the bytes lie in host memory anyway, and XXH32 is one serial recurrence per
+    // frame (xxhash.c:269-275) that a host core runs ~3 x faster than the GPU's single hashing warp — so a helper thread hashes
+    // them while the GPU works.  Device-resident calls keep the GPU kernel (xxh32.cu).
+    XxhState hsum{}; bool hsum_on = false;
     DevBuf dict_stage;
 };
 constexpr size_t HIST_MAX = 65536;
@@ -246,7 +249,6 @@ size_t b2lz4_destroy(b2lz4_ctx* ctx) {
     if (ctx->d_small) cudaFree(ctx->d_small);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_frag) cudaFreeHost(ctx->h_frag);
-    if (ctx->h_xxh) cudaFreeHost(ctx->h_xxh);
     for (auto& v : ctx->ev) if (v) cudaEventDestroy(v);
     if (ctx->ev_in) cudaEventDestroy(ctx->ev_in);
     if (ctx->ev_sum) cudaEventDestroy(ctx->ev_sum);
@@ -645,43 +647,42 @@ static size_t ensure_lanes(b2lz4_ctx* ctx, int want) {
         ctx->n_lanes = k + 1;
     }
     for (int k = 0; k < ctx->n_lanes; ++k) ctx->lanes[k]->prefs = ctx->prefs;
-    if (multi_dev(ctx) && !ctx->h_xxh) {
-        cudaError_t e = cudaHostAlloc((void**)&ctx->h_xxh, sizeof(XxhState), cudaHostAllocPortable | cudaHostAllocMapped);
-        if (e != cudaSuccess) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "cudaHostAlloc: %s", cudaGetErrorString(e)); cudaGetLastError(); return err_code(E_cudaFailure); }
-    }
     cudaSetDevice(ctx->device);
     return 0;
 }
-// running content checksum of a host-buffer call: on one device it runs on the parent's second stream (stream order =
-// chunk order); across devices it hops from lane to lane through events, the state kept in pinned host memory
-struct SumChain {
-    b2lz4_ctx* ctx; cudaEvent_t prev = nullptr; uint32_t launches = 0;
-    void reset() {
-        ctx->sum_host = multi_dev(ctx);
-        if (ctx->sum_host) {
-            XxhState z{}; z.v[0] = XP1 + XP2; z.v[1] = XP2; z.v[2] = 0; z.v[3] = 0u - XP1;    // xxhash.c:437-449
-            *ctx->h_xxh = z;
-        } else { cudaSetDevice(ctx->device); B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st2, &ctx->d_small->xxh); ++launches; }
+extern "C++" {
+// ---- XXH32 streaming state on the host (XXH32_reset / XXH32_update / XXH32_digest, xxhash.c:437-554), same XxhState as the kernels
+static void hsum_reset(XxhState& s) { s = XxhState{}; s.v[0] = XP1 + XP2; s.v[1] = XP2; s.v[2] = 0; s.v[3] = 0u - XP1; }
+static void hsum_update(XxhState& s, const uint8_t* p, size_t n) {
+    s.total_len += (uint32_t)n;
+    s.large |= (uint32_t)((n >= 16) | (s.total_len >= 16));
+    if (s.memsize + n < 16) { memcpy((uint8_t*)s.mem + s.memsize, p, n); s.memsize += (uint32_t)n; return; }
+    if (s.memsize) {
+        const uint32_t take = 16 - s.memsize;
+        memcpy((uint8_t*)s.mem + s.memsize, p, take);
+        for (int k = 0; k < 4; ++k) s.v[k] = xxh32_round(s.v[k], s.mem[k]);
+        p += take; n -= take; s.memsize = 0;
     }
-    // hashes p[0, len) (device memory of lane `ln`) after `after` (an event on the lane's stream, or null); records ln->ev_sum
-    cudaError_t update(b2lz4_ctx* ln, const uint8_t* p, size_t len, cudaEvent_t after) {
-        cudaError_t e;
-        if (ctx->sum_host) {
-            if ((e = cudaSetDevice(ln->device)) != cudaSuccess) return e;
-            if (after && (e = cudaStreamWaitEvent(ln->st2, after, 0)) != cudaSuccess) return e;
-            if (prev && (e = cudaStreamWaitEvent(ln->st2, prev, 0)) != cudaSuccess) return e;
-            B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ln->st2, p, len, nullptr, nullptr, ctx->h_xxh);
-            if ((e = cudaEventRecord(ln->ev_sum, ln->st2)) != cudaSuccess) return e;
-            prev = ln->ev_sum;
-        } else {
-            if (after && (e = cudaStreamWaitEvent(ctx->st2, after, 0)) != cudaSuccess) return e;
-            B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st2, p, len, nullptr, nullptr, &ctx->d_small->xxh);
-            if ((e = cudaEventRecord(ln->ev_sum, ctx->st2)) != cudaSuccess) return e;
-        }
-        ++launches;
-        return cudaSuccess;
+    uint32_t v1 = s.v[0], v2 = s.v[1], v3 = s.v[2], v4 = s.v[3];
+    for (; n >= 16; p += 16, n -= 16) {
+        uint32_t w[4]; memcpy(w, p, 16);
+        v1 = xxh32_round(v1, w[0]); v2 = xxh32_round(v2, w[1]); v3 = xxh32_round(v3, w[2]); v4 = xxh32_round(v4, w[3]);
     }
-};
+    s.v[0] = v1; s.v[1] = v2; s.v[2] = v3; s.v[3] = v4;
+    if (n) { memcpy(s.mem, p, n); s.memsize = (uint32_t)n; }
+}
+static uint32_t hsum_digest(const XxhState& s) {
+    uint32_t h = s.large ? xxh32_merge(s.v[0], s.v[1], s.v[2], s.v[3]) : s.v[2] + XP5;
+    h += s.total_len;
+    return xxh32_tail(h, (const uint8_t*)s.mem, s.memsize);
+}
+// runs f on a helper thread (or right here when no thread is to be had)
+template <typename F> static std::future<void> run_aside(F f) {
+    try { return std::async(std::launch::async, f); }
+    catch (...) { f(); std::promise<void> p; p.set_value(); return p.get_future(); }
+}
+}  // extern "C++"
+
 #define LANE_CU(L, call)                                                                           \
     do { cudaError_t e_ = (call);                                                                  \
          if (e_ != cudaSuccess) { snprintf(ctx->cuda_err, sizeof ctx->cuda_err, "%s: %s (%s:%d)", #call, \
@@ -720,8 +721,14 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     // linked blocks: every chunk goes to its lane with the 64 KB of the stream in front of it (the input is all here, in host
     // memory); in front of the first chunk lies the dictionary (first batch of a frame) or the tail of the batches before
     const std::vector<uint8_t>& front = (hmode == HOSTC_BLOCKS) ? ctx->tail : ctx->dict;
-    SumChain sc{ctx};
-    if (sum && hmode != HOSTC_BLOCKS) sc.reset();
+    std::future<void> hashing;                             // content checksum: the input is hashed on a helper thread meanwhile
+    if (sum) {
+        if (hmode != HOSTC_BLOCKS) hsum_reset(ctx->hsum);
+        ctx->hsum_on = true;
+        XxhState* st = &ctx->hsum; const uint8_t* p8 = (const uint8_t*)src;
+        hashing = run_aside([st, p8, n]() { hsum_update(*st, p8, n); });
+    }
+    struct Joiner { std::future<void>& f; ~Joiner() { if (f.valid()) f.wait(); } } joiner{hashing};   // never outlives the call: src is the caller's
     std::vector<uint8_t> ix_blocks, ix_chains;             // index entries gathered from the chunks
     struct Frag { size_t off; uint32_t nb, nc, chain_base; };
     std::vector<Frag> frags;
@@ -748,7 +755,6 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
         const size_t pad = linked ? HIST_MAX : 0;
         LANE_CU(ln, ln->stage_in.ensure(pad + len + 16));
         LANE_CU(ln, ln->stage_out.ensure(b2lz4_compress_bound(len, &pr) + 16));
-        if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // the checksum pass of the lane's previous chunk
         uint8_t* din = (uint8_t*)ln->stage_in.p + pad;
         uint32_t hist = 0;
         if (linked) {
@@ -762,11 +768,6 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
             LANE_CU(ln, cudaMemcpyAsync(din - own, (const uint8_t*)src + off - own, own + len, cudaMemcpyHostToDevice, ln->st));
         } else
         LANE_CU(ln, cudaMemcpyAsync(din, (const uint8_t*)src + off, len, cudaMemcpyHostToDevice, ln->st));
-        if (sum) {                                                              // serial XXH32 in chunk order
-            LANE_CU(ln, cudaEventRecord(ln->ev_in, ln->st));
-            LANE_CU(ln, sc.update(ln, din, len, ln->ev_in));
-            LANE_CU(ln, cudaSetDevice(ln->device));
-        }
         ln->stats = b2lz4_stats{};
         ln->dict_id = ctx->dict_id;
         size_t e = compress_launch(ln, din, len, (uint8_t*)ln->stage_out.p, ln->stage_out.cap,
@@ -801,8 +802,7 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     }
     for (size_t i = nchunks > (size_t)L ? nchunks - L : 0; i < nchunks; ++i) { r = complete(i); if (r) return r; }
     for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st));
-    launches += sc.launches;
-    if (sum && multi_dev(ctx)) for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st2));
+    if (hashing.valid()) hashing.wait();
     CU(cudaSetDevice(ctx->device));
     if (!whole && linked) {                                                     // what the next batch's first blocks may reach back into
         std::vector<uint8_t> t;
@@ -812,7 +812,6 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
         ctx->tail.swap(t);
     }
     if (!whole) {
-        if (sum) CU(cudaStreamSynchronize(ctx->st2));
         ctx->stats.n_blocks = blocks_total; ctx->stats.n_chains = chains_total; ctx->stats.kernel_launches = launches;
         ctx->stats.ms_main = ms_main; ctx->stats.ms_total = ms_total; ctx->stats.bytes_in = n; ctx->stats.bytes_out = o;
         return o;
@@ -960,6 +959,19 @@ size_t b2lz4_decompress_host(b2lz4_ctx* ctx, const void* src_, size_t n, void* d
     HostFrame f;
     const bool ok = n >= (size_t)HEADER_MIN && host_scan(src, n, ctx->prefs.use_index != 0, f);
     const size_t per_group = ok && f.block_size ? std::max<size_t>(1, pipe_chunk(ctx, (size_t)f.blocks.size() * f.block_size, f.block_size) / f.block_size) : 0;
+    if (ok && f.desc.block_independent && !ctx->dict.empty() && !f.blocks.empty()) {
+        // independent blocks + dictionary: block by block (b2lz4_decompress_blocks_host), then the frame's own checks
+        b2lz4_frame_info info{};
+        info.block_size_id = f.desc.block_size_id; info.block_independent = 1; info.block_checksum = f.desc.block_checksum;
+        info.content_checksum = f.desc.content_checksum; info.block_size = f.block_size;
+        const size_t b0 = f.blocks[0].off;
+        r = b2lz4_decompress_blocks_host(ctx, &info, src + b0, f.end_blocks - b0, dst, cap, B2LZ4_STREAM_FIRST);
+        if (b2lz4_is_error(r)) return r;
+        if (f.desc.content_checksum) { uint32_t h = 0; size_t e = b2lz4_content_checksum(ctx, &h); if (e) return e; if (h != f.stored_sum) return err_code(E_contentChecksum_invalid); }
+        if (f.desc.has_content_size && f.desc.content_size != r) return err_code(E_frameSize_wrong);
+        if (consumed) *consumed = f.consumed;
+        return r;
+    }
     if (!ok || !f.desc.block_independent || f.blocks.size() <= per_group)
         return decompress_host_whole(ctx, src_, n, dst, cap, consumed);           // linked frames, small frames, anything odd
     r = decompress_host_groups(ctx, src, f, per_group, dst, cap, HOSTC_FRAME);
@@ -982,8 +994,10 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
     r = ensure_lanes(ctx, L); if (r) return r;
     const uint32_t bc = f.desc.block_checksum ? 4u : 0u;
     const bool sum = f.desc.content_checksum != 0;
-    SumChain sc{ctx};
-    if (sum && hmode != HOSTC_BLOCKS) sc.reset();
+    // content checksum: every group's output is hashed on a helper thread, in order, once its copy to the host is done
+    std::future<void> hashing;
+    struct Joiner { std::future<void>& f; ~Joiner() { if (f.valid()) f.wait(); } } joiner{hashing};       // dst is the caller's
+    if (sum) { if (hmode != HOSTC_BLOCKS) hsum_reset(ctx->hsum); ctx->hsum_on = true; }
     FrameDesc gd{}; gd.block_size_id = f.desc.block_size_id; gd.block_independent = 1; gd.block_checksum = f.desc.block_checksum;
     uint8_t ghdr[HEADER_MAX]; const uint32_t ghs = header_write(ghdr, gd);
     uint8_t* out = (uint8_t*)dst;
@@ -1023,7 +1037,6 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
         LANE_CU(ln, cudaSetDevice(ln->device));
         LANE_CU(ln, ln->stage_in.ensure(G.frame_len + 16));
         LANE_CU(ln, ln->stage_out.ensure(G.out_cap + 16));
-        if (sum) LANE_CU(ln, cudaStreamWaitEvent(ln->st, ln->ev_sum, 0));          // checksum pass over the lane's previous output
         uint8_t* din = (uint8_t*)ln->stage_in.p;
         const uint32_t zero = 0;
         LANE_CU(ln, cudaMemcpyAsync(din, ghdr, ghs, cudaMemcpyHostToDevice, ln->st));
@@ -1045,7 +1058,12 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
         if (used != G.frame_len) return err_code(E_decompressionFailed);
         if (o + c > cap) return err_code(E_dstMaxSize_tooSmall);
         if (c) LANE_CU(ln, cudaMemcpyAsync(out + o, ln->stage_out.p, c, cudaMemcpyDeviceToHost, ln->st));
-        if (sum && c) LANE_CU(ln, sc.update(ln, (const uint8_t*)ln->stage_out.p, c, nullptr));   // the lane's decode has completed (host waited)
+        if (sum && c) {
+            LANE_CU(ln, cudaEventRecord(ln->ev_sum, ln->st));                       // the copy above has landed when this event has
+            XxhState* st = &ctx->hsum; const uint8_t* p8 = out + o; const size_t len = c; cudaEvent_t ev = ln->ev_sum;
+            std::shared_future<void> prev = hashing.valid() ? hashing.share() : std::shared_future<void>();
+            hashing = run_aside([st, p8, len, ev, prev]() { if (prev.valid()) prev.wait(); cudaEventSynchronize(ev); hsum_update(*st, p8, len); });
+        }
         launches += ln->stats.kernel_launches; ms_main += ln->stats.ms_main; ms_total += ln->stats.ms_total;
         chains_total += ln->stats.n_chains;
         o += c;
@@ -1057,10 +1075,8 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
     }
     for (size_t g = ngroups > (size_t)L ? ngroups - L : 0; g < ngroups; ++g) { r = complete(g); if (r) return r; }
     for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st));
-    launches += sc.launches;
-    if (sum && multi_dev(ctx)) for (int k = 0; k < L; ++k) LANE_CU(ctx->lanes[k], cudaStreamSynchronize(ctx->lanes[k]->st2));
+    if (hashing.valid()) hashing.wait();
     CU(cudaSetDevice(ctx->device));
-    if (sum && !whole) CU(cudaStreamSynchronize(ctx->st2));
     if (sum && whole) {
         uint32_t h = 0; r = b2lz4_content_checksum(ctx, &h); if (r) return r;
         if (h != f.stored_sum) return err_code(E_contentChecksum_invalid);      // lz4frame.c:1734-1745
@@ -1078,14 +1094,7 @@ size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, voi
     size_t r = set_device(ctx); if (r) return r;
     ctx->stats = b2lz4_stats{};
     if (n == 0) {                                                   // nothing to emit, but the checksum may have to restart
-        if ((flags & B2LZ4_STREAM_FIRST) && ctx->prefs.content_checksum) {
-            if (multi_dev(ctx)) { r = ensure_lanes(ctx, 1); if (r) return r; SumChain sc{ctx}; sc.reset(); }
-            else {
-                ctx->sum_host = false;
-                B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ctx->d_small->xxh);
-                CU(cudaStreamSynchronize(ctx->st));
-            }
-        }
+        if ((flags & B2LZ4_STREAM_FIRST) && ctx->prefs.content_checksum) { hsum_reset(ctx->hsum); ctx->hsum_on = true; }
         return 0;
     }
     // the batch goes through the same chunk pipeline as a whole frame (lanes, and every device of b2lz4_set_devices)
@@ -1095,14 +1104,7 @@ size_t b2lz4_compress_blocks_host(b2lz4_ctx* ctx, const void* src, size_t n, voi
 size_t b2lz4_content_checksum(b2lz4_ctx* ctx, uint32_t* out) {
     if (!ctx || !out) return err_code(E_GENERIC);
     size_t r = set_device(ctx); if (r) return r;
-    if (ctx->sum_host && ctx->h_xxh) {                              // state in pinned host memory: finish the lanes, digest on the host
-        for (int k = 0; k < ctx->n_lanes; ++k) CU(cudaStreamSynchronize(ctx->lanes[k]->st2));
-        const XxhState s = *ctx->h_xxh;                              // xxhash.c:529-554
-        uint32_t h = s.large ? xxh32_merge(s.v[0], s.v[1], s.v[2], s.v[3]) : s.v[2] + XP5;
-        h += s.total_len;
-        *out = xxh32_tail(h, (const uint8_t*)s.mem, s.memsize);
-        return 0;
-    }
+    if (ctx->hsum_on) { *out = hsum_digest(ctx->hsum); return 0; }   // host-buffer stream: hashed on the host (xxhash.c:529-554)
     Small* ds = ctx->d_small;
     CU(cudaStreamSynchronize(ctx->st2));
     B2_LAUNCH(xxh32_digest_kernel, 1, 32, 0, ctx->st, &ds->xxh, &ds->hash_out, nullptr, nullptr);
@@ -1154,10 +1156,49 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     size_t r = set_device(ctx); if (r) return r;
     Small* ds = ctx->d_small;
     if (flags & B2LZ4_STREAM_FIRST) {
-        ctx->ring_pos = 65536; ctx->ring_hist = 0; ctx->sum_host = false;
-        if (info->content_checksum) B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ds->xxh);
+        ctx->ring_pos = 65536; ctx->ring_hist = 0;
+        if (info->content_checksum) { B2_LAUNCH(xxh32_reset_kernel, 1, 32, 0, ctx->st, &ds->xxh); hsum_reset(ctx->hsum); }
     }
+    // independent blocks without a dictionary: the output is hashed on the host (group pipeline and the small-batch path below
+    // alike); linked / legacy / dictionary streams keep the running checksum on the device
+    const bool host_sum = !legacy && info->block_independent && ctx->dict.empty();
+    ctx->hsum_on = host_sum && info->content_checksum;
     if (n == 0) { CU(cudaStreamSynchronize(ctx->st)); return 0; }
+    if (!legacy && info->block_independent && !ctx->dict.empty()) {
+        // independent blocks WITH a dictionary (what `lz4 -D` writes for single-block inputs, LZ4F_compressFrame_usingCDict,
+        // lz4frame.c:392-395): every block may reach into the dictionary but not into its neighbours.  Each block is decoded
+        // on its own as "a linked frame of one block whose history is the dictionary" — dictionary frames are small-message
+        // territory, one launch sequence per block is fine.
+        const uint32_t bs = block_size_of(info->block_size_id), bcs = info->block_checksum ? 4u : 0u, dl = (uint32_t)ctx->dict.size();
+        FrameDesc d{}; d.block_size_id = info->block_size_id; d.block_independent = 0; d.block_checksum = info->block_checksum ? 1u : 0u;
+        uint8_t hdr[HEADER_MAX]; const uint32_t hs = header_write(hdr, d); const uint32_t zero = 0;
+        CU(ctx->dict_stage.ensure(HIST_MAX + bs + 16));
+        uint8_t* dout = (uint8_t*)ctx->dict_stage.p + HIST_MAX;
+        CU(cudaMemcpyAsync(dout - dl, ctx->dict.data(), dl, cudaMemcpyHostToDevice, ctx->st));
+        const uint8_t* s8 = (const uint8_t*)src; size_t ip = 0, o = 0;
+        const uint32_t keep_index = ctx->prefs.use_index; ctx->prefs.use_index = 0;
+        while (ip < n) {
+            if (n - ip < 4) { ctx->prefs.use_index = keep_index; return err_code(E_decompressionFailed); }
+            const uint32_t cs = ld_le32(s8 + ip) & 0x7FFFFFFFu;
+            if (cs == 0 || cs > bs || n - ip - 4 < (size_t)cs + bcs) { ctx->prefs.use_index = keep_index; return err_code(cs > bs ? E_maxBlockSize_invalid : E_decompressionFailed); }
+            const size_t one = 4 + (size_t)cs + bcs;
+            CU(ctx->stage_in.ensure(hs + one + 4 + 16));
+            uint8_t* din = (uint8_t*)ctx->stage_in.p;
+            CU(cudaMemcpyAsync(din, hdr, hs, cudaMemcpyHostToDevice, ctx->st));
+            CU(cudaMemcpyAsync(din + hs, s8 + ip, one, cudaMemcpyHostToDevice, ctx->st));
+            CU(cudaMemcpyAsync(din + hs + one, &zero, 4, cudaMemcpyHostToDevice, ctx->st));
+            size_t used = 0;
+            r = decompress_device_impl(ctx, din, hs + one + 4, dout, bs, &used, dl, SCAN_BATCH);
+            if (b2lz4_is_error(r)) { ctx->prefs.use_index = keep_index; return r; }
+            if (o + r > cap) { ctx->prefs.use_index = keep_index; return err_code(E_dstMaxSize_tooSmall); }
+            if (info->content_checksum && r) B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st, dout, r, nullptr, nullptr, &ds->xxh);
+            if (r) CU(cudaMemcpyAsync((uint8_t*)dst + o, dout, r, cudaMemcpyDeviceToHost, ctx->st));
+            CU(cudaStreamSynchronize(ctx->st));
+            o += r; ip += one;
+        }
+        ctx->prefs.use_index = keep_index;
+        return o;
+    }
     if (!legacy && info->block_independent) {
         // independent blocks: the same group pipeline as a whole frame (lanes; every device of b2lz4_set_devices)
         HostFrame f;
@@ -1213,10 +1254,11 @@ size_t b2lz4_decompress_blocks_host(b2lz4_ctx* ctx, const b2lz4_frame_info* info
     ctx->prefs.use_index = keep_index;
     if (b2lz4_is_error(r)) return r;
     if (consumed != hs + n + 4) return err_code(E_decompressionFailed);   // an EndMark inside the batch: not whole blocks
-    if (info->content_checksum && r) B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st, dout, r, nullptr, nullptr, &ds->xxh);
+    if (info->content_checksum && r && !host_sum) B2_LAUNCH(xxh32_stream_kernel, 1, 256, 0, ctx->st, dout, r, nullptr, nullptr, &ds->xxh);
     if (r) CU(cudaMemcpyAsync(dst, dout, r, cudaMemcpyDeviceToHost, ctx->st));
     CU(cudaStreamSynchronize(ctx->st));
     CU(cudaGetLastError());
+    if (info->content_checksum && r && host_sum) hsum_update(ctx->hsum, (const uint8_t*)dst, r);
     if (linked) {
         ctx->ring_pos += r;
         ctx->ring_hist = (uint32_t)std::min<size_t>(65536, (size_t)ctx->ring_hist + r);

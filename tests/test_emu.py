@@ -195,6 +195,8 @@ def test_emu_dictionary_frames_both_ways(emu_replay, ref, lz4_cli, manifest, gen
             assert dict_decompress(emu_replay, ours, dic, len(d) + 64, 999) == d
             if ref is not None:
                 assert dict_decompress(ref, ours, dic, len(d) + 64, 1000) == d
+                indep = dict_compress(ref, d, dic, 4, 1, 1, did)                  # independent blocks + dictionary (what `lz4 -D` writes for one block)
+                assert dict_decompress(emu_replay, indep, dic, len(d) + 64, 4096) == d
                 theirs = dict_compress(ref, d, dic, 4, 0, 1, did)
                 assert ours[:len(theirs[:11]) if did else 7] == theirs[:11 if did else 7]        # same header bytes
                 assert dict_decompress(emu_replay, theirs, dic, len(d) + 64) == d

@@ -200,6 +200,8 @@ def test_dictionary_frames_both_ways(replay, ref, lz4_cli, manifest, gen, tmp_pa
             assert dict_decompress(replay, ours, dic, len(d) + 64, 99999) == d
             if ref is not None:
                 assert dict_decompress(ref, ours, dic, len(d) + 64, 100000) == d
+                indep = dict_compress(ref, d, dic, 4, 1, 1, did)                  # independent blocks + dictionary (what `lz4 -D` writes for one block)
+                assert dict_decompress(replay, indep, dic, len(d) + 64, 4096) == d
                 theirs = dict_compress(ref, d, dic, 4, 0, 1, did)
                 assert ours[:11 if did else 7] == theirs[:11 if did else 7]
                 assert dict_decompress(replay, theirs, dic, len(d) + 64) == d
