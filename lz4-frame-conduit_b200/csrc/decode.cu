@@ -78,6 +78,7 @@ __device__ B2_NOINLINE void walk_blocks_df(const uint8_t* __restrict__ src, uint
     s.layout_known = 0; s.walk_pending = 0; s.df = 1;
     DfState st; st.bad_key = 0xFFFFFFFFFFFFFFFFull; st.produced = 0; st.total_out = 0; st.n_tickets = 0; st.n_units = 0;
     st.ticket_links = 0; st.ticket_units = 0; st.ticket_tk = 0; st.pad = 0;
+    for (int i = 0; i < 12; ++i) st.prof[i] = 0;
     *W.st = st;
 }
 

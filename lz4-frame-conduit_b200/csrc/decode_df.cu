@@ -320,11 +320,11 @@ size_t decode_df_smem_bytes(uint32_t warps) { return sizeof(DfCta) + DF_WIN_BYTE
 
 // a finished ticket: publish it, then retire every finished ticket at the low end (clear their bits, raise the watermark)
 __device__ __forceinline__ void df_retire(DfCta* C, const DfShared& S, uint32_t t, uint64_t hi, bool solo, uint32_t lane) {
-    __threadfence_block();
+    DF_FENCE();
     __syncwarp();
     if (lane == 0) {
         C->ring_hi[t % DF_RING] = hi;
-        __threadfence_block();
+        DF_FENCE();
         ((volatile uint32_t*)C->ring_done)[t % DF_RING] = solo ? 2u : 1u;
     }
     for (;;) {
@@ -347,11 +347,11 @@ __device__ __forceinline__ void df_retire(DfCta* C, const DfShared& S, uint32_t 
             }
             __syncwarp();
             if (lane == 0) {
-                __threadfence_block();
+                DF_FENCE();
                 *(volatile unsigned long long*)&C->final_below = F;
-                __threadfence_block();
+                DF_FENCE();
                 *(volatile uint32_t*)&C->lowest = low;
-                __threadfence_block();
+                DF_FENCE();
                 atomicExch(&C->lock, 0u);
             }
         }
@@ -425,27 +425,34 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                 if (last_of_block) { tok_end = br.csize; out_end = br.usize; }
                 else { const uint2 z = W.tk[t + 1u]; tok_end = z.x; out_end = z.y; }
             }
+#ifdef B2_DF_PROF
+            const long long pt0 = clock64();
+#endif
             // ---- flow control: the ticket's bytes must fit the bitmap window behind the watermark, its done flag the ring;
             // a ticket too large for the window runs when it is the lowest one (everything in front of it is final then)
             uint32_t solo = 0;
             if (lane == 0) {
+                uint32_t nap = DF_NAP_MIN;
                 for (;;) {
                     const uint32_t low = *(volatile uint32_t*)&C->lowest;
                     const unsigned long long F = *(volatile unsigned long long*)&C->final_below;
                     const bool fits = blk_out + out_end <= F + DF_HALF;
                     if (t == low) { solo = fits ? 0u : 1u; break; }
                     if (t - low < DF_RING && fits) break;
-                    __nanosleep(64);
+                    __nanosleep(nap); nap = nap < 4u * DF_NAP_MAX ? nap * 2u : 4u * DF_NAP_MAX;
                 }
             }
             solo = __shfl_sync(FULL_MASK, solo, 0);
-            __threadfence_block();
+            DF_FENCE();
+#ifdef B2_DF_PROF
+            const long long pt1 = clock64(); uint32_t p_rounds = 0, p_naps = 0;
+#endif
             uint32_t e = 0, produced = 0;
             if (br.stored) {                                                  // a raw block inside a linked frame: later blocks may read it
                 if (blk_out + br.csize > dst_cap) e = E_dstMaxSize_tooSmall;
                 else {
                     group_copy(dst + blk_out, src + br.src_off, br.csize, lane, 32);
-                    if (!solo) { __threadfence_block(); __syncwarp(); df_mark_warp(S, blk_out, blk_out + br.csize, lane); }
+                    if (!solo) { DF_FENCE(); __syncwarp(); df_mark_warp(S, blk_out, blk_out + br.csize, lane); }
                     produced = br.csize;
                 }
             } else {
@@ -460,20 +467,24 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                 // output of the frame, and of earlier batches in front of the buffer (lz4frame.c:1286-1349)
                 if (linked) { const uint64_t h = blk_out + hist; cu.reach = h > 0x40000000ull ? 0x40000000u : (uint32_t)h; }
                 else cu.reach = 0u;
-                cu.df = S; cu.abs0 = (int64_t)blk_out; cu.solo = solo != 0u;
+                cu.df = S; cu.abs0 = (int64_t)blk_out; cu.solo = solo != 0u; cu.prof_rounds = cu.prof_naps = 0; cu.prof_cyc[0] = cu.prof_cyc[1] = cu.prof_cyc[2] = cu.prof_cyc[3] = 0;
                 for (;;) {
                     e = decode_piece<true>(cu, last_of_block);
                     if (e != DEC_PAUSED) break;
                     // a huge overlapping match: wait for its source window [d - off, d), fill, publish
                     __syncwarp();
                     const int64_t a = (int64_t)blk_out + (int64_t)cu.p_dst - (int64_t)cu.p_off;
-                    if (!solo) { while (!df_ready_warp(S, a, (int64_t)blk_out + cu.p_dst, lane)) __nanosleep(64); __threadfence_block(); }
+                    if (!solo) { uint32_t nap = DF_NAP_MIN; while (!df_ready_warp(S, a, (int64_t)blk_out + cu.p_dst, lane)) { __nanosleep(nap); nap = nap < DF_NAP_MAX ? nap * 2u : DF_NAP_MAX; } DF_FENCE(); }
                     warp_match_overlap(cu.dp + cu.p_dst, cu.p_off, cu.p_ml, lane);
-                    if (!solo) { __threadfence_block(); __syncwarp(); df_mark_warp(S, blk_out + cu.p_dst, blk_out + cu.p_dst + cu.p_ml, lane); }
+                    if (!solo) { DF_FENCE(); __syncwarp(); df_mark_warp(S, blk_out + cu.p_dst, blk_out + cu.p_dst + cu.p_ml, lane); }
                     __syncwarp();
                     if (cu.p_done) { e = 0; break; }
                 }
                 produced = cu.op - out;
+#ifdef B2_DF_PROF
+                p_rounds = cu.prof_rounds; p_naps = cu.prof_naps;
+                if (lane == 0) for (int q = 0; q < 4; ++q) atomicAdd(&W.st->prof[6 + q], (unsigned long long)cu.prof_cyc[q]);
+#endif
                 if (e == 0 && (produced != out_end - out || cu.ip != tok_end)) e = E_decompressionFailed;
                 if (e && cu.oend < block_size && e != E_dstMaxSize_tooSmall) e = E_dstMaxSize_tooSmall;   // ran out of destination
             }
@@ -482,7 +493,18 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                 else atomicAdd(&W.st->produced, (unsigned long long)produced);
             }
             // (after an error the bytes may be wrong, but later tickets must not wait for them for ever: retire all the same)
+#ifdef B2_DF_PROF
+            const long long pt2 = clock64();
+#endif
             df_retire(C, S, t, blk_out + out_end, solo != 0u, lane);
+#ifdef B2_DF_PROF
+            if (lane == 0) {
+                const long long pt3 = clock64();
+                atomicAdd(&W.st->prof[0], (unsigned long long)(pt1 - pt0)); atomicAdd(&W.st->prof[1], (unsigned long long)(pt2 - pt1));
+                atomicAdd(&W.st->prof[2], (unsigned long long)(pt3 - pt2)); atomicAdd(&W.st->prof[3], 1ull);
+                atomicAdd(&W.st->prof[4], (unsigned long long)p_rounds); atomicAdd(&W.st->prof[5], (unsigned long long)p_naps);
+            }
+#endif
         }
     }
 }

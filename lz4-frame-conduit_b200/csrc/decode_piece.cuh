@@ -5,6 +5,10 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#ifndef B2_DEC_LANE_CAP
+#define B2_DEC_LANE_CAP 24
+#endif
+
 namespace b2 {
 
 // ------------------------------------------------------------------------------------------------
@@ -27,10 +31,28 @@ struct Cursor {            // what the warp knows about the piece it is decoding
                            // independent piece: -piece_start;  linked: bytes of earlier output in front of the block
     // dataflow mode (decode_df.cu): this piece is one ticket of a unit that a whole CTA decodes; bytes in front of it are
     // written by OTHER warps of the CTA.  abs0 = offset of the owning block's first output byte in the destination buffer.
-    DfShared df;
+ DfShared df;
     int64_t abs0;
+    uint32_t prof_rounds, prof_naps;   // -DB2_DF_PROF: match rounds / of them without progress
+    uint32_t prof_cyc[4];              // ... cycles: parse, literals, chase, match rounds
     bool solo;             // the piece runs alone (every earlier byte is final, nobody reads the map): no waits, no marks
 };
+
+// the CTA-scope fence of the dataflow hand-over (tuning builds: -DB2_DF_FENCE=0 none — measurement only, not correct;
+// 2 = device scope)
+#ifndef B2_DF_FENCE
+#define B2_DF_FENCE 1
+#endif
+#ifndef B2_DF_PIPECOPY
+#define B2_DF_PIPECOPY 1      // per-lane match copies of the dataflow decoder issue all their loads before their stores
+#endif
+#if B2_DF_FENCE == 0
+#define DF_FENCE() do {} while (0)
+#elif B2_DF_FENCE == 2
+#define DF_FENCE() __threadfence()
+#else
+#define DF_FENCE() __threadfence_block()
+#endif
 
 // ---- dataflow helpers.  The CTA keeps, in shared memory, one bit per output byte for a sliding window of the unit's
 // output (circular, DF_WIN_BYTES long) and a watermark below which every byte is final.  A writer stores its bytes,
@@ -124,6 +146,26 @@ __device__ __forceinline__ void lane_match(uint8_t* d, uint32_t off, uint32_t n)
 __device__ __forceinline__ void lane_match_from(uint8_t* d, const uint8_t* s, uint32_t off, uint32_t n) {
     uint32_t r = 0;
     for (uint32_t k = 0; k < n; ++k) { d[k] = s[r]; r = (r + 1 == off) ? 0u : r + 1; }
+}
+
+// Latency-first per-lane copy of n <= LANE_CAP bytes for the dataflow decoder, where a copy sits on a chain of dependent
+// copies and its source usually comes from L2 (another warp wrote it): EVERY load is issued before the first store, so the
+// copy costs one memory round trip instead of one per four bytes.  period = 0: plain copy from s; else the window
+// [s, s + period) is replicated.  (More instructions than lane_copy for short copies: not for the throughput-bound path.)
+__device__ __forceinline__ void lane_copy_pipelined(uint8_t* d, const uint8_t* s, uint32_t n, uint32_t period) {
+    uint32_t v[(B2_DEC_LANE_CAP + 3) / 4];
+    #pragma unroll
+    for (int j = 0; j < (B2_DEC_LANE_CAP + 3) / 4; ++j) v[j] = 0u;
+    uint32_t r = 0;
+    #pragma unroll
+    for (int k = 0; k < B2_DEC_LANE_CAP; ++k) {
+        if ((uint32_t)k < n) {
+            v[k >> 2] |= (uint32_t)s[period ? r : (uint32_t)k] << (8 * (k & 3));
+            r = (r + 1u == period) ? 0u : r + 1u;
+        }
+    }
+    #pragma unroll
+    for (int k = 0; k < B2_DEC_LANE_CAP; ++k) if ((uint32_t)k < n) d[k] = (uint8_t)(v[k >> 2] >> (8 * (k & 3)));
 }
 
 // Warp-cooperative match copy (long matches): the source window [d - off, d) is final.
@@ -231,6 +273,9 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
     int32_t wb = 0; bool win_ok = false;                                    // window = stream bytes [wb, wb + 256)
     bool finished = false, paused = false;
     while (!finished) {
+#ifdef B2_DF_PROF
+        const long long q0 = clock64();
+#endif
         if (DF && ip >= pend && !ends_block) {                              // the piece's last sequence took the short path
             if (ip != pend || op != opend) err = E_decompressionFailed;
             break;
@@ -402,6 +447,9 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
             my_op = op0 + x - sz;
         }
 
+#ifdef B2_DF_PROF
+        const long long q1 = clock64();
+#endif
         // ---- literals: lane i copies the literals of sequence i; long runs use the whole warp
         {
             const bool act = lane < n && my_ll != 0;
@@ -415,7 +463,7 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 group_copy_small(dp + o, sp + l, len, lane, 32);
             }
             if (DF && !solo) {                                              // literals never wait: publish them at once
-                __threadfence_block();
+                DF_FENCE();
                 __syncwarp();
                 if (act && my_ll <= LANE_CAP) df_mark(c.df, (uint64_t)(abs0 + my_op), (uint64_t)(abs0 + my_op) + my_ll);
                 longm = longm0;
@@ -427,6 +475,9 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
             }
         }
         __syncwarp();
+#ifdef B2_DF_PROF
+        const long long q2 = clock64();
+#endif
         // ---- matches, in rounds
         if (!DF || solo) {
             const uint32_t my_mop = my_op + my_ll;
@@ -485,23 +536,31 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                     if (!__any_sync(FULL_MASK, hop)) break;
                 }
             }
+#ifdef B2_DF_PROF
+            const long long q3 = clock64();
+#endif
             const int64_t xb = xa + my_span;
             const uint8_t* const my_src = dp + (xa - abs0);
+            uint32_t nap = DF_NAP_MIN;                                        // a waiting warp must not eat the issue slots of the one it waits for
             while (pending) {
                 const bool mine = (pending >> lane) & 1u;
                 const bool small = my_ml <= LANE_CAP;
                 // a lane asks about short source windows itself; long ones (rare) are looked at by the whole warp, first one first
                 const bool ready = mine && my_span <= 256u && df_ready(c.df, xa, xb);
                 if (ready && small) {
-                    __threadfence_block();
+                    DF_FENCE();
+#if B2_DF_PIPECOPY
+                    lane_copy_pipelined(dp + my_mop, my_src, my_ml, my_off >= my_ml ? 0u : my_off);
+#else
                     if (my_off >= my_ml) lane_copy(dp + my_mop, my_src, my_ml); else lane_match_from(dp + my_mop, my_src, my_off, my_ml);
+#endif
                 }
                 const uint32_t rb = __ballot_sync(FULL_MASK, ready && small);
                 uint32_t lb = __ballot_sync(FULL_MASK, ready && !small);     // long matches whose sources are there
                 const uint32_t wide = __ballot_sync(FULL_MASK, mine && my_span > 256u);
                 bool progressed = rb != 0u;
                 if (rb) {
-                    __threadfence_block();
+                    DF_FENCE();
                     if (ready && small) df_mark(c.df, (uint64_t)(abs0 + my_mop), (uint64_t)(abs0 + my_mop) + my_ml);
                     pending &= ~rb;
                 }
@@ -514,21 +573,27 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                     const int g = __ffs(lb) - 1; lb &= lb - 1;
                     const uint32_t W = __shfl_sync(FULL_MASK, my_mop, g), ml_g = __shfl_sync(FULL_MASK, my_ml, g), off_g = __shfl_sync(FULL_MASK, my_off, g);
                     const uint8_t* m = dp + (__shfl_sync(FULL_MASK, xa, g) - abs0);
-                    __threadfence_block();
+                    DF_FENCE();
                     if (off_g >= ml_g) group_copy_small(dp + W, m, ml_g, lane, 32);
                     else {                                                  // overlapping: period replication from the final window
                         uint32_t r = lane % off_g; const uint32_t step = 32u % off_g;
                         for (uint32_t i = lane; i < ml_g; i += 32) { dp[W + i] = m[r]; r += step; if (r >= off_g) r -= off_g; }
                     }
-                    __threadfence_block();
+                    DF_FENCE();
                     __syncwarp();
                     df_mark_warp(c.df, (uint64_t)(abs0 + W), (uint64_t)(abs0 + W) + ml_g, lane);
                     pending &= ~(1u << g);
                     progressed = true;
                 }
                 __syncwarp();
-                if (!progressed) __nanosleep(32);
+#ifdef B2_DF_PROF
+                ++c.prof_rounds; if (!progressed) ++c.prof_naps;
+#endif
+                if (!progressed) { __nanosleep(nap); nap = nap < DF_NAP_MAX ? nap * 2u : DF_NAP_MAX; } else nap = DF_NAP_MIN;
             }
+#ifdef B2_DF_PROF
+            { const long long q4 = clock64(); c.prof_cyc[0] += (uint32_t)(q1 - q0); c.prof_cyc[1] += (uint32_t)(q2 - q1); c.prof_cyc[2] += (uint32_t)(q3 - q2); c.prof_cyc[3] += (uint32_t)(q4 - q3); }
+#endif
         }
     }
     c.ip = ip; c.op = op;

@@ -74,6 +74,13 @@ constexpr uint32_t DF_BATCH = 32u;          // sequences per ticket (one per lan
 constexpr uint32_t DF_WIN_BYTES = 512u << 10;   // output window covered by the CTA's "final bytes" bitmap (64 KB of shared memory)
 constexpr uint32_t DF_WIN_MASK = DF_WIN_BYTES / 32u - 1u;
 constexpr uint32_t DF_HALF = DF_WIN_BYTES / 2u; // a ticket is handed out when its output ends within this much of the watermark
+#ifndef B2_DF_NAP_MIN
+#define B2_DF_NAP_MIN 64
+#endif
+#ifndef B2_DF_NAP_MAX
+#define B2_DF_NAP_MAX 1024
+#endif
+constexpr uint32_t DF_NAP_MIN = B2_DF_NAP_MIN, DF_NAP_MAX = B2_DF_NAP_MAX;   // back-off of a waiting warp, ns
 constexpr uint32_t DF_RING = 128u;          // tickets between the lowest unfinished and the newest handed out (done flags)
 struct DfHead { uint32_t exit, out; };      // chain from one position of a group: packed (kind, sequences, where it leaves), bytes produced
 struct DfShared {                           // per-CTA dataflow state in shared memory (decode_df_kernel)
@@ -84,6 +91,7 @@ struct DfState {
     unsigned long long bad_key;             // min over failures of (block << 8 | Err); all ones = none
     unsigned long long produced, total_out;
     uint32_t n_tickets, n_units, ticket_links, ticket_units, ticket_tk, pad;
+    unsigned long long prof[12];             // -DB2_DF_PROF: cycles spent per phase of decode_df_kernel, summed over warps (tools/foreign_speed.py prints them)
 };
 struct DfWork {                             // device workspaces of the dataflow path (sized by the host from the scan's needs)
     uint32_t* grp_base;                     // [blocks + 1] first group of every block

@@ -288,6 +288,15 @@ size_t b2lz4_set_dict(b2lz4_ctx* ctx, const void* dict, size_t n, uint32_t dict_
     return 0;
 }
 
+// tuning builds (-DB2_DF_PROF): cycle counters of the last dataflow decode; zeros otherwise.  Not part of include/b200lz4.h.
+size_t b2lz4_debug_df_prof(b2lz4_ctx* ctx, unsigned long long* out8) {
+    if (!ctx || !out8) return err_code(E_GENERIC);
+    size_t r = set_device(ctx); if (r) return r;
+    CU(cudaStreamSynchronize(ctx->st));
+    CU(cudaMemcpy(out8, ctx->d_small->dfst.prof, 12 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 size_t b2lz4_last_stats(const b2lz4_ctx* ctx, b2lz4_stats* out) {
     if (!ctx || !out) return err_code(E_GENERIC);
     *out = ctx->stats;

@@ -58,5 +58,12 @@ with pkg.Codec(0, use_index=0) as c:
                 assert torch.equal(d_out[:n], d_in), name + ": output differs"
         res[name] = {"GBps": round(n / best / 1e9, 2), "ms_total": round(best * 1e3, 3), "ms_decode": round(main, 3),
                      "ratio": round(n / len(fr), 3), "blocks": st.n_blocks, "pieces": st.n_chains, "retries": st.retries, "wall_ms_last": round(dt * 1e3, 2)}
+        if os.environ.get("B2_DF_PROF"):
+            pr = (C.c_ulonglong * 12)()
+            c.lib.b2lz4_debug_df_prof.argtypes = [C.c_void_p, C.c_void_p]; c.lib.b2lz4_debug_df_prof.restype = C.c_size_t
+            c.lib.b2lz4_debug_df_prof(c.h, pr)
+            if pr[3]:
+                res[name]["prof"] = {"tickets": pr[3], "cyc_flow_per_ticket": pr[0] / pr[3], "cyc_decode_per_ticket": pr[1] / pr[3],
+                                     "cyc_retire_per_ticket": pr[2] / pr[3], "rounds_per_ticket": pr[4] / pr[3], "idle_rounds_per_ticket": pr[5] / pr[3], "cyc_parse": pr[6] / pr[3], "cyc_literals": pr[7] / pr[3], "cyc_chase": pr[8] / pr[3], "cyc_rounds": pr[9] / pr[3]}
         print(name, res[name], flush=True)
 print(json.dumps(res))
