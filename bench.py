@@ -297,7 +297,7 @@ def foreign_leg(torch, pkg, codec, lib, host_in, d_in, n):
             "e2e_decompress_GBps": n / t_host / 1e9, "bit_exact": bool(ok)}
 
 
-def sharded_leg(torch, pkg, gen, n_dev, seg_mib=512):
+def sharded_leg(torch, pkg, gen, n_dev, seg_mib=1024):
     """BASELINE.json configs 3 and 5 through ONE context whose host-buffer calls shard the blocks of ONE frame over n_dev
     GPUs by block index (b2lz4_set_devices; no collective: blocks are independent) and reassemble them in order on the
     host.  The stream is never resident: it is produced, compressed, decompressed and compared one pinned segment at a time
