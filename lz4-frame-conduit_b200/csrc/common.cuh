@@ -26,6 +26,18 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
     return __funnelshift_r(lo, w[1], sh);
 }
 
+// ... of memory the kernel only reads (the encoder's input): explicit global loads through the read-only path — a pointer
+// rebuilt from an integer is a GENERIC pointer to the compiler (LD instead of LDG)
+__device__ __forceinline__ uint32_t ldg32(const uint32_t* p) { return __ldg(p); }
+__device__ __forceinline__ uint32_t ld32u_ro(const uint8_t* p) {
+    uintptr_t a = (uintptr_t)p;
+    const uint32_t* w = (const uint32_t*)(a & ~(uintptr_t)3);
+    uint32_t sh = (uint32_t)(a & 3u) * 8u;
+    uint32_t lo = __ldg(w);
+    if (sh == 0) return lo;
+    return __funnelshift_r(lo, __ldg(w + 1), sh);
+}
+
 // Copy n bytes with every thread of a group (nthreads threads, this one is `tid`).  dst/src may have
 // any alignment and must not overlap.  Bulk part: 16-byte stores to the aligned destination; a misaligned
 // source is read as the two aligned 16-byte chunks that hold the bytes and re-aligned with funnel shifts

@@ -14,6 +14,7 @@
 // (lz4_Block_format.md:108-129: last 5 bytes literal, last match starts >= 12 bytes before the end,
 // inputs < 13 bytes are literal-only, offsets <= 65535) and the stored-block rule of the frame layer
 // (a block is stored raw iff it does not compress to fewer bytes, lz4frame.c:746-752).
+#include <type_traits>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -21,9 +22,24 @@ namespace b2 {
 
 constexpr uint32_t HSIZE = 1u << ENC_HLOG;
 
-size_t find_emit_smem_bytes() { return (size_t)ENC_SMEM_WARPS * HSIZE * sizeof(uint16_t); }
+#ifndef B2_ENC_WIN
+#define B2_ENC_WIN 0          // 1 = the 128 positions of a stride-1 step take their own bytes from a shared-memory copy of the step window
+                              // (measured on B200: 48.9 vs 58.9 GB/s — the kernel is bound by instruction issue, the window costs instructions)
+#endif
+constexpr uint32_t ENC_WIN_WORDS = 44;     // bytes T0 - 4 .. T0 + 127 + 12 + 19 (+ alignment) of a step: what probe, verify and the second measuring pass read at the positions
+size_t find_emit_smem_bytes() { return (size_t)ENC_SMEM_WARPS * HSIZE * sizeof(uint16_t) + (B2_ENC_WIN ? (size_t)ENC_WARPS * ENC_WIN_WORDS * 4u : 0u); }
+
+// the aligned word that holds *pp: in the step window (shared memory) or in global memory
+template <bool WIN> __device__ __forceinline__ const uint32_t* pos_words(const uint8_t* pp, const uint32_t* wwin, uintptr_t gA) {
+    if (WIN) return wwin + ((((uintptr_t)pp & ~(uintptr_t)3) - gA) >> 2);
+    return (const uint32_t*)((uintptr_t)pp & ~(uintptr_t)3);
+}
 size_t find_emit_gtab_bytes(uint32_t grid) { return (size_t)grid * (ENC_WARPS - ENC_SMEM_WARPS) * HSIZE * sizeof(uint16_t); }
 
+#if B2_PTX
+__device__ __forceinline__ uint32_t lds_u16(uint32_t saddr) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(saddr) : "memory"); return v; }
+__device__ __forceinline__ void sts_u16(uint32_t saddr, uint16_t v) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(saddr), "h"(v) : "memory"); }
+#endif
 __device__ __forceinline__ uint32_t hash4(uint32_t v) { return (v * 2654435761u) >> (32 - ENC_HLOG); }
 
 __device__ __forceinline__ uint32_t len_bytes(uint32_t v) {      // extra length bytes for a field value v
@@ -138,6 +154,11 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
     // lives in L1/L2: 32 warps per SM fit that way (192 KB of tables), and measured against 24 warps with every
     // table in shared memory the occupancy wins (59 vs 55.5 GB/s)
     const uint32_t wid = threadIdx.x >> 5;
+#if B2_ENC_WIN
+    uint32_t* const wwin = (uint32_t*)(s_tab + (size_t)ENC_SMEM_WARPS * HSIZE) + wid * ENC_WIN_WORDS;   // this warp's step window
+#else
+    uint32_t* const wwin = nullptr;
+#endif
     uint16_t* tab = wid < (uint32_t)ENC_SMEM_WARPS ? s_tab + wid * HSIZE
                   : gtab + ((size_t)blockIdx.x * (ENC_WARPS - ENC_SMEM_WARPS) + (wid - ENC_SMEM_WARPS)) * HSIZE;
 
@@ -146,8 +167,18 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 #define B2_ENC_TAB_CG 0      // measured: .cg table accesses 45.7 GB/s, cached ones 47.3 GB/s
 #endif
     const bool tab_global = wid >= (uint32_t)ENC_SMEM_WARPS;
+#ifndef B2_ENC_TABSPLIT
+#define B2_ENC_TABSPLIT 0     // (measured: 55.3 vs 58.9 GB/s)  1 = every table access is written twice, through a shared and through a global pointer (warp-uniform
+                              // choice): LDS / STS and LDG / STG instead of generic LD / ST through one pointer
+#endif
+#if B2_ENC_TABSPLIT && B2_PTX
+    const uint32_t stab = (uint32_t)__cvta_generic_to_shared(s_tab + (wid < (uint32_t)ENC_SMEM_WARPS ? wid : 0u) * HSIZE);   // (only used when !tab_global)
+    #define TAB_LD(p) (tab_global ? (uint32_t)*(p) : lds_u16(stab + 2u * (uint32_t)((p) - tab)))
+    #define TAB_ST(p, v) do { if (tab_global) *(p) = (v); else sts_u16(stab + 2u * (uint32_t)((p) - tab), (uint16_t)(v)); } while (0)
+#else
     #define TAB_LD(p) ((B2_ENC_TAB_CG && tab_global) ? (uint32_t)__ldcg((const unsigned short*)(p)) : (uint32_t)*(p))
     #define TAB_ST(p, v) do { if (B2_ENC_TAB_CG && tab_global) __stcg((unsigned short*)(p), (unsigned short)(v)); else *(p) = (v); } while (0)
+#endif
     for (;;) {
         uint32_t s = 0;
         if (lane == 0) s = atomicAdd(ticket, 1u);
@@ -190,7 +221,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                     #pragma unroll
                     for (int k = 0; k < 4; ++k) {
                         const uint32_t pp = q + (32u * k + lane) * ENC_PRIME_STRIDE;
-                        const uint32_t vv = pp < b0 ? ld32u(base + pp) : 0u;
+                        const uint32_t vv = pp < b0 ? ld32u_ro(base + pp) : 0u;
                         // inside a run the neighbouring position has the same hash: only the later one needs the slot
                         const uint32_t vn = __shfl_down_sync(FULL_MASK, vv, 1);
                         if (pp < b0 && (lane == 31u || vn != vv || pp + ENC_PRIME_STRIDE >= b0)) TAB_ST(tab + hash4(vv), (uint16_t)(pp - d0));
@@ -205,11 +236,11 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 for (int k = 0; k < 8; ++k) {
                     const uint32_t pp = b0 + 32u * k + lane;
                     if (pp + 4u <= b1) {
-                        const uint32_t vv = ld32u(base + pp);
+                        const uint32_t vv = ld32u_ro(base + pp);
                         const uint32_t cl = TAB_LD(tab + hash4(vv));
                         int32_t cc = (int32_t)(((pp - d0) & ~0xFFFFu) | cl);
                         if ((uint32_t)cc >= pp - d0) cc -= 65536;
-                        if (cc >= 0 && ld32u(base + d0 + cc) == vv) hit = true;
+                        if (cc >= 0 && ld32u_ro(base + d0 + cc) == vv) hit = true;
                     }
                 }
                 if (__any_sync(FULL_MASK, hit)) {                           // compressible: the whole history, oldest first
@@ -239,6 +270,22 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
             const uint32_t sl = miss < 3u ? miss : miss < 8u ? 3u : miss < 16u ? 4u : 5u;
             const uint32_t span = 128u << sl;
             if (lane < 2u && T0 + span + 128u * (lane + 1u) <= usize) prefetch_l1(base + T0 + span + 128u * lane);   // next step's input
+            // ---- 0. stride-1 steps (compressible input: almost all of them): the bytes at and around the 128 positions are loaded
+            // ONCE, coalesced, into the warp's window in shared memory; probe, verify and the second measuring pass read their
+            // position-side words there (44 shared-memory words instead of 28 global loads per lane).  Words are fetched whole, so
+            // only words that hold a byte of [base, base + usize) are touched (same-word slack, as everywhere in this kernel).
+            const bool use_win = B2_ENC_WIN && sl == 0u;
+            uintptr_t gA = 0;
+            if (use_win) {
+                gA = ((uintptr_t)(base + T0) - 4u) & ~(uintptr_t)3;
+                const uintptr_t lo = (uintptr_t)base & ~(uintptr_t)3, hi = (uintptr_t)(base + usize);
+                __syncwarp();
+                for (uint32_t w = lane; w < ENC_WIN_WORDS; w += 32u) {
+                    const uintptr_t a = gA + 4u * w;
+                    wwin[w] = (a >= lo && a < hi) ? ldg32((const uint32_t*)a) : 0u;
+                }
+                __syncwarp();
+            }
             // ---- 1. probe
             uint32_t v[4], h[4], rel[4]; int32_t c[4]; bool ok[4];
             #pragma unroll
@@ -246,7 +293,13 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 const uint32_t p = T0 + ((32u * k + lane) << sl);
                 ok[k] = p < limit;
                 rel[k] = p - d0;
-                v[k] = ok[k] ? ld32u(base + p) : 0u;
+                if (use_win) {
+                    const uint8_t* pp = base + p;
+                    const uint32_t* w = pos_words<true>(pp, wwin, gA);
+                    const uint32_t sh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
+                    v[k] = ok[k] ? __funnelshift_r(w[0], w[1], sh) : 0u;
+                } else
+                v[k] = ok[k] ? ld32u_ro(base + p) : 0u;
                 h[k] = hash4(v[k]);
             }
             #pragma unroll
@@ -260,6 +313,9 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
             // most matches are fully measured here (forward length up to 12, backward up to 4) and the serial
             // selection below rarely has to touch memory
             uint32_t H[4], pk[4];
+            auto verify = [&](auto WINC) {
+            constexpr bool WIN = decltype(WINC)::value;
+            #define PW(i) (WIN ? pw[(i)] : ldg32(pw + (i)))      /* window: shared memory; else global */
             #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 bool hit = false;
@@ -268,11 +324,11 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                     const uint8_t* cp = base + d0 + c[k];
                     const uint8_t* pp = base + d0 + rel[k];
                     const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
-                    const uint32_t* pw = (const uint32_t*)((uintptr_t)pp & ~(uintptr_t)3);
+                    const uint32_t* pw = pos_words<WIN>(pp, wwin, gA);
                     const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
                     const bool bk_ok = c[k] >= 4;                             // 4 bytes in front of the candidate are inside the sub-block
-                    const uint32_t c0 = cw[0], c1 = cw[1], c2 = cw[2], c3 = csh ? cw[3] : 0u, cm = bk_ok ? cw[-1] : 0u;
-                    const uint32_t p0 = pw[0], p1 = pw[1], p2 = pw[2], p3 = psh ? pw[3] : 0u, pm = bk_ok ? pw[-1] : 0u;
+                    const uint32_t c0 = ldg32(cw), c1 = ldg32(cw + 1), c2 = ldg32(cw + 2), c3 = csh ? ldg32(cw + 3) : 0u, cm = bk_ok ? ldg32(cw - 1) : 0u;
+                    const uint32_t p0 = PW(0), p1 = PW(1), p2 = PW(2), p3 = psh ? PW(3) : 0u, pm = bk_ok ? PW(-1) : 0u;
                     const uint32_t x1 = __funnelshift_r(c0, c1, csh) ^ __funnelshift_r(p0, p1, psh);
                     if (x1 == 0u) {
                         hit = true;
@@ -311,15 +367,15 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                             const uint8_t* cp = base + d0 + (pv & 0x3FFFFFu) + 12u;
                             const uint8_t* pp = base + d0 + rl + 12u;
                             const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
-                            const uint32_t* pw = (const uint32_t*)((uintptr_t)pp & ~(uintptr_t)3);
+                            const uint32_t* pw = pos_words<WIN>(pp, wwin, gA);
                             const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
                             // only words that hold bytes below matchlimit + 3 are touched (same-word slack only)
                             const uint32_t nw = (room - 12u + 3u) >> 2;                      // words of interest: 1..4+
-                            const uint32_t c0 = cw[0], p0 = pw[0];
-                            const uint32_t c1 = cw[1], p1 = pw[1];
-                            const uint32_t c2 = nw > 1u ? cw[2] : 0u, p2 = nw > 1u ? pw[2] : 0u;
-                            const uint32_t c3 = nw > 2u ? cw[3] : 0u, p3 = nw > 2u ? pw[3] : 0u;
-                            const uint32_t c4 = (nw > 3u && csh) ? cw[4] : 0u, p4 = (nw > 3u && psh) ? pw[4] : 0u;
+                            const uint32_t c0 = ldg32(cw), p0 = PW(0);
+                            const uint32_t c1 = ldg32(cw + 1), p1 = PW(1);
+                            const uint32_t c2 = nw > 1u ? ldg32(cw + 2) : 0u, p2 = nw > 1u ? PW(2) : 0u;
+                            const uint32_t c3 = nw > 2u ? ldg32(cw + 3) : 0u, p3 = nw > 2u ? PW(3) : 0u;
+                            const uint32_t c4 = (nw > 3u && csh) ? ldg32(cw + 4) : 0u, p4 = (nw > 3u && psh) ? PW(4) : 0u;
                             const uint32_t x0 = __funnelshift_r(c0, c1, csh) ^ __funnelshift_r(p0, p1, psh);
                             const uint32_t x1 = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, psh);
                             const uint32_t x2 = __funnelshift_r(c2, c3, csh) ^ __funnelshift_r(p2, p3, psh);
@@ -335,6 +391,9 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                     }
                 }
             }
+            #undef PW
+            };
+            if (use_win) verify(std::true_type{}); else verify(std::false_type{});
             // ---- 2c. lazy evaluation, lane-parallel: a short match is dropped when one of the next three positions holds a
             // match at least two bytes longer — the greedy parse would otherwise take the short one and step over the
             // start of the long one (tools/enc_model.c LAZY: ratio +4 % on log-like, +1 % on text, 15 % fewer sequences)
@@ -406,7 +465,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                                 const uint32_t qq = lp + len + lane * 4u;
                                 const uint32_t avail = matchlimit > qq ? matchlimit - qq : 0u;
                                 if (avail) {
-                                    const uint32_t xx = ld32u(base + qq) ^ ld32u(base + lc + len + lane * 4u);
+                                    const uint32_t xx = ld32u_ro(base + qq) ^ ld32u_ro(base + lc + len + lane * 4u);
                                     nbytes = xx ? (uint32_t)(__ffs(xx) - 1) >> 3 : 4u;
                                     if (nbytes > avail) nbytes = avail;
                                 }
@@ -421,7 +480,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                                     #pragma unroll
                                     for (int j = 3; j >= 0; --j) {
                                         if (4u * j < avail) {
-                                            const uint32_t xx = ld32u(pa + 4 * j) ^ ld32u(pb + 4 * j);
+                                            const uint32_t xx = ld32u_ro(pa + 4 * j) ^ ld32u_ro(pb + 4 * j);
                                             if (xx) nbytes = 4u * j + ((uint32_t)(__ffs(xx) - 1) >> 3);
                                         }
                                     }
