@@ -6,6 +6,7 @@
 #include "../../tools/emu/emu_cuda.h"
 #define B2_NOINLINE __attribute__((noinline))
 #define B2_PTX 0
+struct B2Range { explicit B2Range(const char*) {} };
 #else
 #include <cuda_runtime.h>
 // shared memory is declared through these so that the emulator can give every CTA its own copy
@@ -15,4 +16,8 @@
 #define B2_LAUNCH(kern, grid, block, smem, stream, ...) kern<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
 #define B2_NOINLINE __noinline__
 #define B2_PTX 1
+// NVTX ranges around the host-side phases (batch submit = H2D + kernels, batch completion = wait + D2H): visible in Nsight
+// Systems / ncu timelines, a no-op without a profiler attached (header-only NVTX v3)
+#include <nvtx3/nvToolsExt.h>
+struct B2Range { explicit B2Range(const char* name) { nvtxRangePushA(name); } ~B2Range() { nvtxRangePop(); } };
 #endif

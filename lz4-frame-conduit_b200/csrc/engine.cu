@@ -414,6 +414,7 @@ static size_t compress_finish(b2lz4_ctx* ctx, size_t n) {
 
 size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* d_dst, size_t cap) {
     if (!ctx || (!d_src && n) || !d_dst) return err_code(E_GENERIC);
+    B2Range range("b2lz4_compress_device");
     size_t r = set_device(ctx); if (r) return r;
     ctx->stats = b2lz4_stats{};
     uint32_t hist = 0;
@@ -569,6 +570,7 @@ static size_t decompress_device_impl(b2lz4_ctx* ctx, const void* d_src, size_t n
     if (consumed) *consumed = 0;
     if (!ctx || !d_src || (!d_dst && cap)) return err_code(E_GENERIC);
     if (n < (size_t)HEADER_MIN) return err_code(E_frameHeader_incomplete);
+    B2Range range("b2lz4 decompress (device buffers)");
     size_t r = set_device(ctx); if (r) return r;
     if (!launched0) ctx->stats = b2lz4_stats{};
     static uint8_t* dummy = nullptr;
@@ -758,6 +760,7 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
     CU(cudaEventRecord(t0, ctx->st));
 
     auto submit = [&](size_t i) -> size_t {
+        B2Range range("b2lz4 compress: chunk H2D + kernels");
         b2lz4_ctx* ln = ctx->lanes[i % L];
         const size_t off = plan[i] * bs, len = std::min(plan[i + 1] * bs, n) - off;
         LANE_CU(ln, cudaSetDevice(ln->device));
@@ -785,6 +788,7 @@ static size_t compress_host_impl(b2lz4_ctx* ctx, const void* src, size_t n, void
         return 0;
     };
     auto complete = [&](size_t i) -> size_t {
+        B2Range range("b2lz4 compress: chunk wait + D2H");
         b2lz4_ctx* ln = ctx->lanes[i % L];
         const size_t off = plan[i] * bs, len = std::min(plan[i + 1] * bs, n) - off;
         LANE_CU(ln, cudaSetDevice(ln->device));
@@ -1016,6 +1020,7 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
     std::vector<Group> groups(ngroups);
 
     auto submit = [&](size_t g) -> size_t {
+        B2Range range("b2lz4 decompress: group H2D + kernels");
         b2lz4_ctx* ln = ctx->lanes[g % L];
         const size_t b0 = plan[g], b1 = plan[g + 1];
         const size_t s0 = f.blocks[b0].off, s1 = b1 < nb ? f.blocks[b1].off : f.end_blocks;
@@ -1058,6 +1063,7 @@ static size_t decompress_host_groups(b2lz4_ctx* ctx, const uint8_t* src, const H
         return 0;
     };
     auto complete = [&](size_t g) -> size_t {
+        B2Range range("b2lz4 decompress: group wait + D2H");
         b2lz4_ctx* ln = ctx->lanes[g % L];
         const Group& G = groups[g];
         size_t used = 0;

@@ -29,6 +29,12 @@ def run(lib, name, size):
     print(f"{name}: conduit compress {size / tc / 1e9:.2f} GB/s, conduit decompress {size / td / 1e9:.2f} GB/s, frame {c} B (ratio {size / c:.3f})", flush=True)
     return c
 run(ours, "b200 LZ4F_* (Tier 1)", n)
+# compressYieldImmediately (Conduit.hsc:364-425): a fresh LZ4F_compressBound(len)-sized buffer per upstream ByteString (the replay
+# mallocs it like allocaBytes does), here with 32 KB ByteStrings — conduit's default file chunk
+ours.ref_conduit_compress_yi(src, min(n, 64 << 20), comp, cap, 32768)
+cy, ty = t(lambda: ours.ref_conduit_compress_yi(src, n, comp, cap, 32768))
+assert cy < (1 << 62), f"compressYieldImmediately failed with code {(1 << 64) - cy}"
+print(f"b200 LZ4F_* (Tier 1): conduit compressYieldImmediately {n / ty / 1e9:.2f} GB/s, frame {cy} B", flush=True)
 if ref is not None:
     m = min(n, 256 << 20)
     c = run(ref, "reference library, 1 thread", m)                                          # comp now holds a reference-made frame
