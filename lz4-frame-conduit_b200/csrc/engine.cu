@@ -490,7 +490,10 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
         (uint32_t*)ctx->stored.p, (PieceOut*)ctx->outs.p, &ds->ticket_dec, ds->walk, hist);
     B2_LAUNCH(copy_stored_kernel, ctx->sm_count * 8, 256, 0, ctx->st, d_src, d_dst, cap, &ds->fi, (const Piece*)ctx->pieces.p,
                                                              (const Chain*)ctx->chains.p, (const uint32_t*)ctx->stored.p);
-    if (mode & SCAN_DF) {                         // every one of these returns at once unless the scan chose the dataflow path
+    // every one of these returns at once unless the scan chose the dataflow path; without workspaces the scan cannot choose
+    // it (it answers ERROR_allocation_failed + need_*), so a context that never met such a frame does not pay the launches
+    const bool df_launch = (mode & SCAN_DF) && ctx->df_groups;
+    if (df_launch) {
         const BlockRef* bl = (const BlockRef*)ctx->blocks.p;
         B2_LAUNCH(df_links_kernel, ctx->sm_count * 3, DF_WARPS * 32, df_links_smem_bytes(), ctx->st, d_src, n, &ds->fi, bl, W);
         B2_LAUNCH(df_stitch_kernel, std::max(1u, std::min((cap_tables + 127u) / 128u, 1024u)), 128, 0, ctx->st, d_src, &ds->fi, bl, W);
