@@ -133,6 +133,23 @@ size_t b2lz4_content_checksum(b2lz4_ctx* ctx, uint32_t* out);
 size_t b2lz4_xxh32_device(b2lz4_ctx* ctx, const void* d_src, size_t n, uint32_t* out);
 size_t b2lz4_xxh32_host(b2lz4_ctx* ctx, const void* src, size_t n, uint32_t* out);
 
+/* ---- XXH32 (seed 0) of n_ranges byte ranges [offs[i], offs[i] + lens[i]) of the device buffer d_src[0, n_src) — the
+ * frame layer's block checksums — by an entry point that ALLOCATES NOTHING: no context, no cudaMalloc / cudaFree /
+ * cudaMallocHost, no stream or event creation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Descriptors and results pass through a file-scope __device__ array of 1 MiB + 256 B (csrc/noalloc.cu) that every
+ * GPU which loads the library holds until the process exits; hence the limit B2LZ4_STATIC_MAX_RANGES per call, beyond
+ * which the call fails with ERROR_srcSize_tooLarge (as does a range that leaves the buffer) and
+ * b2lz4_static_last_error() says why.  offs / lens / out are HOST arrays of n_ranges entries; `stream` is a
+ * cudaStream_t of `device` (NULL = the default stream) on which the work is queued; the call returns after it has
+ * finished and leaves the caller's current device unchanged.  All calls on a device share the one array, which keeps the
+ * last call's contents: calls of one process are serialised inside, but work queued against the array by other means
+ * while a call runs would race. */
+#define B2LZ4_STATIC_MAX_RANGES 65536u
+size_t b2lz4_xxh32_ranges_static(int device, void* stream, const void* d_src, size_t n_src,
+                                 const uint64_t* offs, const uint32_t* lens, uint32_t n_ranges, uint32_t* out);
+const char* b2lz4_static_last_error(void);   /* text of this thread's last failure of the call above ("" if none) */
+
 size_t b2lz4_last_stats(const b2lz4_ctx* ctx, b2lz4_stats* out);
 
 #ifdef __cplusplus

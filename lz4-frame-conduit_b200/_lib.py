@@ -63,6 +63,9 @@ SYMBOLS = {
     "b2lz4_xxh32_device": (_sz, [_vp, _vp, _sz, _u32p]),
     "b2lz4_xxh32_host": (_sz, [_vp, _vp, _sz, _u32p]),
     "b2lz4_last_stats": (_sz, [_vp, C.POINTER(Stats)]),
+    # no counterpart in the reference: allocation-free block checksums, csrc/noalloc.cu
+    "b2lz4_xxh32_ranges_static": (_sz, [C.c_int, _vp, _vp, _sz, C.POINTER(C.c_uint64), _u32p, C.c_uint32, _u32p]),
+    "b2lz4_static_last_error": (C.c_char_p, []),
 }
 
 _lib = None

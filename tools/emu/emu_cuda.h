@@ -154,6 +154,8 @@ static inline const char* cudaGetErrorString(cudaError_t e) { return e == cudaSu
 static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 static inline cudaError_t cudaGetDeviceCount(int* n) { *n = emu::device_count(); return *n ? cudaSuccess : 100; }
 static inline cudaError_t cudaSetDevice(int d) { if (d < 0 || d >= emu::device_count()) return cudaErrorInvalidDevice; emu::current_device() = d; return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int* d) { *d = emu::current_device(); return cudaSuccess; }
+template <typename T> static inline cudaError_t cudaGetSymbolAddress(void** p, T& sym) { *p = (void*)&sym; return cudaSuccess; }   // one "device" image
 static inline cudaError_t cudaDeviceGetAttribute(int* v, cudaDeviceAttr, int) { *v = emu::sm_count(); return cudaSuccess; }
 template <typename F> static inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return cudaSuccess; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, unsigned) { if (!emu::device_count()) return 100; *s = (cudaStream_t)malloc(8); return cudaSuccess; }
