@@ -328,10 +328,15 @@ def sharded_leg(torch, pkg, gen, n_dev, seg_mib=1024):
             if i == 0:
                 h_in.zero_()
             return
-        per = seg // threads
+        # always 16 slices with their own seeds, whatever the number of host cores: the stream (and with it `frame_xxh32`)
+        # must be the same on every box
+        slices = 16
+        per = seg // slices
         fn = gen.b2gen_loglike if kind == "loglike" else gen.b2gen_random
-        ts = [threading.Thread(target=fn, args=(h_in.data_ptr() + k * per, per if k + 1 < threads else seg - k * per,
-                                                (0x10C5 + i) * 64 + k)) for k in range(threads)]
+        def work(k0):
+            for k in range(k0, slices, threads):
+                fn(h_in.data_ptr() + k * per, per if k + 1 < slices else seg - k * per, (0x10C5 + i) * 64 + k)
+        ts = [threading.Thread(target=work, args=(k0,)) for k0 in range(threads)]
         for t in ts: t.start()
         for t in ts: t.join()
 

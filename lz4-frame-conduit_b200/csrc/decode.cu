@@ -309,8 +309,9 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* _
     // (streaming decode in batches: lz4frame.c:1286-1349 keeps the same 64 KB)
     if (fi->err != OK || fi->df) return;
     const uint32_t lane = lane_id();
-    B2_SHARED_ARRAY(uint8_t, s_walk, DEC_WARPS * 1568);                    // per warp: window (272) + 5 link tables (256 each)
+    B2_SHARED_ARRAY(uint8_t, s_walk, DEC_WARPS * (1568 + TILE));           // per warp: window (272) + 5 link tables (256 each) [+ output tile]
     uint8_t* const my_win = s_walk + (threadIdx.x >> 5) * 1568u;
+    uint8_t* const my_tile = s_walk + DEC_WARPS * 1568u + (threadIdx.x >> 5) * TILE;
     for (uint32_t i = lane; i < 5u * 128u; i += 32u) {                       // upper halves of the tables are identity for good
         const uint32_t t = i >> 7, x = 128u + (i & 127u);
         my_win[272u + 256u * t + x] = (uint8_t)x;
@@ -391,7 +392,7 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* _
                 }
             } else {
                 Cursor cu;
-                cu.sp = src + br.src_off; cu.dp = dst + blk_out; cu.win = my_win; cu.src_end = src_end;
+                cu.sp = src + br.src_off; cu.dp = dst + blk_out; cu.win = my_win; cu.tile = my_tile; cu.src_end = src_end;
                 cu.ip = (uint32_t)(pc.src_off - br.src_off); cu.iend = cu.ip + pc.src_len;
                 cu.iend_blk = br.csize;
                 const uint32_t op_rel = (uint32_t)(op - blk_out);

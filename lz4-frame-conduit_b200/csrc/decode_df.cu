@@ -459,7 +459,7 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                 uint64_t oend = blk_out + block_size;
                 if (blk_out >= dst_cap) oend = blk_out; else if (oend > dst_cap) oend = dst_cap;
                 Cursor cu;
-                cu.sp = src + br.src_off; cu.dp = dst + blk_out; cu.win = my_win; cu.src_end = src_end;
+                cu.sp = src + br.src_off; cu.dp = dst + blk_out; cu.win = my_win; cu.tile = nullptr; cu.src_end = src_end;
                 cu.ip = tok; cu.iend = tok_end; cu.iend_blk = br.csize;
                 cu.op = out; cu.oend = (uint32_t)(oend - blk_out); cu.opiece_end = out_end;
                 cu.p_dst = cu.p_off = cu.p_ml = 0; cu.p_done = false;

@@ -8,8 +8,18 @@
 #ifndef B2_DEC_LANE_CAP
 #define B2_DEC_LANE_CAP 24
 #endif
+// Output tile of the one-warp-per-piece decoder (decode.cu), bytes per warp, a power of two; 0 = none.  The last B2_DEC_TILE
+// bytes a warp produced live in shared memory (circular, indexed by the low bits of the global address): literals and matches
+// are written THERE, a match whose source is that recent reads it from there (a shared-memory round trip instead of one
+// through L2 for bytes the warp itself stored a moment ago), and every byte goes to global memory once, in 16-byte rows.
+#ifndef B2_DEC_TILE
+#define B2_DEC_TILE 0
+#endif
 
 namespace b2 {
+
+constexpr uint32_t TILE = B2_DEC_TILE, TILE_MASK = TILE ? TILE - 1u : 0u, TILE_BATCH_MAX = TILE / 2u;
+static_assert((TILE & TILE_MASK) == 0u && (TILE == 0u || TILE >= 1024u), "B2_DEC_TILE: 0 or a power of two >= 1024");
 
 // ------------------------------------------------------------------------------------------------
 // sequence decoder: one warp per chain, pieces in order.
@@ -36,6 +46,7 @@ struct Cursor {            // what the warp knows about the piece it is decoding
     uint32_t prof_rounds, prof_naps;   // -DB2_DF_PROF: match rounds / of them without progress
     uint32_t prof_cyc[4];              // ... cycles: parse, literals, chase, match rounds
     bool solo;             // the piece runs alone (every earlier byte is final, nobody reads the map): no waits, no marks
+    uint8_t* tile;         // B2_DEC_TILE bytes of this warp's shared memory (16-byte aligned), unused in dataflow mode
 };
 
 // the CTA-scope fence of the dataflow hand-over (tuning builds: -DB2_DF_FENCE=0 none — measurement only, not correct;
@@ -223,6 +234,34 @@ __device__ __forceinline__ T ld_cg(const T* p) {
     return v;
 }
 
+
+// ---- output tile (B2_DEC_TILE).  State: the tile holds the bytes [tv, end of the last tiled batch) of the block's output at
+// index (position + lo) & TILE_MASK, lo = low bits of the block's global output address (so that 16-byte rows of the tile are
+// 16-byte rows of global memory); global memory holds everything below fp; tv <= fp always.
+struct TileState { uint8_t* t; uint32_t lo, tv, fp; };
+
+// writes [T.fp, upto) to global memory — whole 16-byte rows only unless `exact`
+__device__ __forceinline__ void tile_flush(TileState& T, uint8_t* dp, uint32_t upto, bool exact, uint32_t lane) {
+    uint32_t lim = upto;
+    if (!exact) lim -= (upto + T.lo) & 15u;
+    if ((int32_t)(lim - T.fp) <= 0) return;
+    uint32_t a = T.fp;
+    uint32_t head = (16u - ((a + T.lo) & 15u)) & 15u;
+    if (head > lim - a) head = lim - a;
+    if (lane < head) dp[a + lane] = T.t[(a + T.lo + lane) & TILE_MASK];
+    a += head;
+    const uint32_t nq = (lim - a) >> 4;
+    for (uint32_t q = lane; q < nq; q += 32u)
+        *(uint4*)(dp + a + 16u * q) = *(const uint4*)(T.t + ((a + T.lo + 16u * q) & TILE_MASK));
+    a += nq << 4;
+    if (lane < lim - a) dp[a + lane] = T.t[(a + T.lo + lane) & TILE_MASK];
+    T.fp = lim;
+}
+// one byte of the block's output at (signed) position pos: from the tile when it is recent enough, else from global memory
+__device__ __forceinline__ uint8_t tile_getb(const TileState& T, const uint8_t* dp, int32_t pos) {
+    return pos >= (int32_t)T.tv ? T.t[((uint32_t)pos + T.lo) & TILE_MASK] : dp[pos];
+}
+
 constexpr uint32_t DEC_PAUSED = 0xFFFFFFFEu;   // decode_piece: stopped in front of a huge overlapping match (see Cursor::p_*)
 constexpr uint32_t HUGE_MATCH = 512u;          // overlapping matches at least this long are filled outside the sequence loop
 constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs the general path
@@ -261,6 +300,9 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
     asm volatile("" : "+r"(i_fast), "+r"(o_fast));                          // keep them in registers (no re-derivation per sequence)
     uint32_t err = 0;
     if (pend == ip) return E_decompressionFailed;                           // empty input (lz4.c:1702)
+    TileState T{};                                                          // (dead code unless B2_DEC_TILE: the tile starts empty)
+    uint32_t t_end = op;                                                    // end of the bytes the copy phases have produced
+    if constexpr (!DF && TILE != 0u) { T.t = c.tile; T.lo = (uint32_t)(uintptr_t)dp & TILE_MASK; T.tv = T.fp = op; }
     // ---- lane-parallel token walk (the common case).  128 consecutive bytes of the stream are examined at once:
     // every lane computes, for 4 byte positions, where the next token would be IF a token started there (one
     // shared-memory byte, two with an extension byte).  Squaring that link table four times (T1, T2, T4, T8, T16)
@@ -450,6 +492,76 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
 #ifdef B2_DF_PROF
         const long long q1 = clock64();
 #endif
+        bool tiled = false;
+        if constexpr (!DF && TILE != 0u) {
+            // a batch goes through the tile when it is small enough to leave the tile's older half in place (a batch that is not
+            // — long runs, a paused huge match — writes global memory directly, after everything before it has been flushed)
+            tiled = !paused && op - op0 <= TILE_BATCH_MAX;
+            if (!tiled) tile_flush(T, dp, t_end, true, lane);
+        }
+        if (tiled) {
+            if ((int32_t)(op - T.tv) > (int32_t)TILE) T.tv = op - TILE;       // what this batch's bytes overwrite is gone
+            uint8_t* const tl = T.t; const uint32_t lo = T.lo;
+            {   // ---- literals into the tile
+                const bool act = lane < n && my_ll != 0;
+                if (act && my_ll <= LANE_CAP) {
+                    const uint32_t di = (my_op + lo) & TILE_MASK;
+                    if (di + my_ll <= TILE) lane_copy(tl + di, sp + my_lit, my_ll);
+                    else for (uint32_t k = 0; k < my_ll; ++k) tl[(di + k) & TILE_MASK] = sp[my_lit + k];
+                }
+                uint32_t longm = __ballot_sync(FULL_MASK, act && my_ll > LANE_CAP);
+                while (longm) {
+                    const int j = __ffs(longm) - 1; longm &= longm - 1;
+                    const uint32_t l = __shfl_sync(FULL_MASK, my_lit, j), o = __shfl_sync(FULL_MASK, my_op, j) + lo;
+                    const uint32_t len = __shfl_sync(FULL_MASK, my_ll, j);
+                    for (uint32_t i = lane; i < len; i += 32u) tl[(o + i) & TILE_MASK] = sp[l + i];
+                }
+            }
+            __syncwarp();
+            {   // ---- matches in rounds, same order rule as below; sources come from the tile when they are recent enough
+                const uint32_t my_mop = my_op + my_ll;
+                const int32_t my_need = (int32_t)(my_ml < my_off ? my_ml : my_off) - (int32_t)my_off;
+                const int32_t my_a = (int32_t)(my_mop - my_off);            // first source byte (negative: history in front of the block)
+                uint32_t pending = __ballot_sync(FULL_MASK, lane < n && my_ml != 0);
+                while (pending) {
+                    const int f = __ffs(pending) - 1;
+                    const uint32_t W = __shfl_sync(FULL_MASK, my_mop, f);
+                    const uint32_t ml_f = __shfl_sync(FULL_MASK, my_ml, f);
+                    if (ml_f > LANE_CAP) {
+                        const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
+                        const int32_t a = (int32_t)(W - off_f);
+                        if (off_f >= ml_f) { for (uint32_t i = lane; i < ml_f; i += 32u) tl[(W + lo + i) & TILE_MASK] = tile_getb(T, dp, a + (int32_t)i); }
+                        else {
+                            uint32_t r = lane % off_f; const uint32_t step = 32u % off_f;
+                            for (uint32_t i = lane; i < ml_f; i += 32u) { tl[(W + lo + i) & TILE_MASK] = tile_getb(T, dp, a + (int32_t)r); r += step; if (r >= off_f) r -= off_f; }
+                        }
+                        pending &= ~(1u << f);
+                    } else {
+                        const bool ready = ((pending >> lane) & 1u) && my_ml <= LANE_CAP &&
+                                           ((int)lane == f || (int64_t)my_mop + my_need <= (int64_t)W);
+                        if (ready) {
+                            const uint32_t di = (my_mop + lo) & TILE_MASK, si = ((uint32_t)my_a + lo) & TILE_MASK;
+                            const bool in_t = my_a >= (int32_t)T.tv;
+                            const bool simple = my_off >= my_ml && di + my_ml <= TILE &&
+                                                (in_t ? si + my_ml <= TILE : my_a + (int32_t)my_ml <= (int32_t)T.tv);
+                            if (simple) lane_copy(tl + di, in_t ? (const uint8_t*)(tl + si) : (const uint8_t*)(dp + my_a), my_ml);
+                            else {
+                                uint32_t r = 0;
+                                for (uint32_t k = 0; k < my_ml; ++k) {
+                                    tl[(di + k) & TILE_MASK] = tile_getb(T, dp, my_a + (int32_t)r);
+                                    r = (r + 1u == my_off) ? 0u : r + 1u;
+                                }
+                            }
+                        }
+                        pending &= ~__ballot_sync(FULL_MASK, ready);
+                    }
+                    __syncwarp();
+                }
+            }
+            t_end = op;
+            tile_flush(T, dp, t_end, false, lane);
+            continue;
+        }
         // ---- literals: lane i copies the literals of sequence i; long runs use the whole warp
         {
             const bool act = lane < n && my_ll != 0;
@@ -595,7 +707,9 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
             { const long long q4 = clock64(); c.prof_cyc[0] += (uint32_t)(q1 - q0); c.prof_cyc[1] += (uint32_t)(q2 - q1); c.prof_cyc[2] += (uint32_t)(q3 - q2); c.prof_cyc[3] += (uint32_t)(q4 - q3); }
 #endif
         }
+        if constexpr (!DF && TILE != 0u) { T.tv = T.fp = t_end = op; }      // this batch went straight to global memory: the tile is empty
     }
+    if constexpr (!DF && TILE != 0u) { __syncwarp(); tile_flush(T, dp, t_end, true, lane); __syncwarp(); }
     c.ip = ip; c.op = op;
     return err ? err : (paused ? DEC_PAUSED : 0u);
 }

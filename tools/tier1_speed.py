@@ -1,7 +1,7 @@
 """GPU box: throughput of the UNMODIFIED conduit's call sequence (oracle/conduit_replay.c: 16 KB LZ4F_compressUpdate calls,
 16 KB+ LZ4F_decompress destinations, pageable host buffers) on the product's LZ4F_* symbols, next to the same replay on the
 reference library (1 thread).  Also decodes a reference-made (linked 64 KB blocks) frame through the same calls.
-usage: python tools/tier1_speed.py [size_mib]"""
+usage: python tools/tier1_speed.py [size_mib] [--only-compress]   (B2LZ4_BATCH_MB=.. for a batch-size sweep of the compress legs)"""
 import ctypes as C, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -12,7 +12,9 @@ pkg = importlib.import_module("lz4-frame-conduit_b200"); pkg.load()
 ours = conftest._bind_replay(C.CDLL(conftest.build_replay_b200()))
 refp = os.path.join(ROOT, "oracle", "_ref", "libref.so")
 ref = conftest._bind_replay(C.CDLL(refp)) if os.path.exists(refp) else None
-n = (int(sys.argv[1]) if len(sys.argv) > 1 else 1024) << 20
+only_compress = "--only-compress" in sys.argv
+argv = [a for a in sys.argv[1:] if not a.startswith("--")]
+n = (int(argv[0]) if argv else 1024) << 20
 gen = C.CDLL(os.path.join(ROOT, "tools", "libb2gen.so")); gen.b2gen_loglike.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
 src = C.create_string_buffer(n); gen.b2gen_loglike(C.addressof(src), n, 0x10C5)
 cap = n + n // 100 + (1 << 20)
@@ -34,7 +36,11 @@ run(ours, "b200 LZ4F_* (Tier 1)", n)
 ours.ref_conduit_compress_yi(src, min(n, 64 << 20), comp, cap, 32768)
 cy, ty = t(lambda: ours.ref_conduit_compress_yi(src, n, comp, cap, 32768))
 assert cy < (1 << 62), f"compressYieldImmediately failed with code {(1 << 64) - cy}"
-print(f"b200 LZ4F_* (Tier 1): conduit compressYieldImmediately {n / ty / 1e9:.2f} GB/s, frame {cy} B", flush=True)
+print(f"b200 LZ4F_* (Tier 1): conduit compressYieldImmediately {n / ty / 1e9:.2f} GB/s, frame {cy} B "
+      f"(batch {os.environ['B2LZ4_BATCH_MB']} MiB, LZ4F_compressBound(32 KB) = {ours.ref_compress_bound(32768) >> 20} MiB)" if hasattr(ours, "ref_compress_bound")
+      else f"b200 LZ4F_* (Tier 1): conduit compressYieldImmediately {n / ty / 1e9:.2f} GB/s, frame {cy} B (batch {os.environ['B2LZ4_BATCH_MB']} MiB)", flush=True)
+if only_compress:
+    sys.exit(0)
 if ref is not None:
     m = min(n, 256 << 20)
     c = run(ref, "reference library, 1 thread", m)                                          # comp now holds a reference-made frame
@@ -56,6 +62,10 @@ if os.path.exists(cli):
             used = C.c_size_t(0)
             for lib, name in ((ours, "b200 LZ4F_decompress"), (ref, "reference library")):
                 if lib is None: continue
+                # first pass: a context that has never seen such a frame (pins its staging, sizes the dataflow workspaces);
+                # second pass: the same process decoding the next such file (staging comes from the pool)
                 d, td_ = t(lambda: lib.ref_conduit_decompress(fr, len(fr), back, n + 64, 65536, C.byref(used)))
                 assert d == m and back.raw[m - 4096:m] == src.raw[m - 4096:m], (name, d)
-                print(f"{name} on a {what} ({m >> 20} MiB): {m / td_ / 1e9:.2f} GB/s", flush=True)
+                d, tw_ = t(lambda: lib.ref_conduit_decompress(fr, len(fr), back, n + 64, 65536, C.byref(used)))
+                assert d == m
+                print(f"{name} on a {what} ({m >> 20} MiB): {m / td_ / 1e9:.2f} GB/s first file, {m / tw_ / 1e9:.2f} GB/s next file", flush=True)
