@@ -26,8 +26,12 @@
  *   - free(NULL) is a no-op; contexts are not thread-safe, distinct contexts are independent.
  * What differs (allowed by the format, lz4_Frame_format.md): frames are always written with independent
  * blocks, LZ4F_default block size means 256 KB, and the encoder works in batches (B2LZ4_BATCH_MB, default
- * 32 MiB, one on the GPU while the next is staged), so LZ4F_compressBound() is larger than the reference's
- * and output arrives in larger pieces, one batch late.
+ * 12 MiB for compression, one on the GPU while the next is staged), so output arrives in larger pieces, one batch late,
+ * and LZ4F_compressBound(srcSize) = the stored size of (2 batches - 1 + srcSize) bytes + 8: about 24 MiB with the
+ * default batch (the reference: one block + srcSize).  It is what ANY single call may have to emit — LZ4F_compressEnd
+ * included, which the reference conduit serves from a buffer of LZ4F_compressBound(19 + 16384) bytes, Conduit.hsc:466-495 —
+ * so it cannot depend on srcSize alone.  The default batch was chosen with a measurement: callers that allocate the bound
+ * per input piece (compressYieldImmediately, Conduit.hsc:385-400) run at the speed of `compress` below 32 MiB.
  * LZ4F_decompress, details a caller may notice (none is used by Conduit.hsc, which only tests the result for 0, error, or
  * "anything else"):
  *   - while decoded bytes are waiting to be handed out, the return value is a hint for the NEXT DESTINATION size (at most

@@ -530,7 +530,11 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                     if (ml_f > LANE_CAP) {
                         const uint32_t off_f = __shfl_sync(FULL_MASK, my_off, f);
                         const int32_t a = (int32_t)(W - off_f);
-                        if (off_f >= ml_f) { for (uint32_t i = lane; i < ml_f; i += 32u) tl[(W + lo + i) & TILE_MASK] = tile_getb(T, dp, a + (int32_t)i); }
+                        if (off_f >= ml_f) {                                   // plain copy; where the source lies is the same question for every lane
+                            if (a >= (int32_t)T.tv) { for (uint32_t i = lane; i < ml_f; i += 32u) tl[(W + lo + i) & TILE_MASK] = tl[((uint32_t)a + lo + i) & TILE_MASK]; }
+                            else if (a + (int32_t)ml_f <= (int32_t)T.tv) { for (uint32_t i = lane; i < ml_f; i += 32u) tl[(W + lo + i) & TILE_MASK] = dp[a + (int32_t)i]; }
+                            else { for (uint32_t i = lane; i < ml_f; i += 32u) tl[(W + lo + i) & TILE_MASK] = tile_getb(T, dp, a + (int32_t)i); }
+                        }
                         else {
                             uint32_t r = lane % off_f; const uint32_t step = 32u % off_f;
                             for (uint32_t i = lane; i < ml_f; i += 32u) { tl[(W + lo + i) & TILE_MASK] = tile_getb(T, dp, a + (int32_t)r); r += step; if (r >= off_f) r -= off_f; }

@@ -27,18 +27,23 @@ namespace {
 
 inline size_t ec(uint32_t e) { return (size_t)0 - (size_t)e; }
 
-size_t batch_bytes() {                       // B2LZ4_BATCH_MB: uncompressed bytes handed to the GPU per call (default 32 MiB:
-                                             // the GPU is done with a batch before the host has copied the next one in)
-    static size_t v = 0;
-    if (!v) {
-        const char* e = getenv("B2LZ4_BATCH_MB");
-        long mb = e ? atol(e) : 32;
-        if (mb < 4) mb = 4;
-        if (mb > 2048) mb = 2048;
-        v = ((size_t)mb << 20) & ~(((size_t)4 << 20) - 1);
-    }
-    return v;
+// uncompressed bytes handed to the GPU per call.  B2LZ4_BATCH_MB sets both directions (4..2048 MiB).  Defaults:
+//   decompression 32 MiB — the GPU is done with a batch before the host has copied the next one in;
+//   compression   12 MiB — measured through the unmodified conduit's call sequence (profiles/r2y_tier1_batch_sweep.txt):
+//     `compress` runs as fast with 12 MiB batches as with 32 (4.9 vs 4.5-5.1 GB/s, the layer is bound by the caller's
+//     copies), and LZ4F_compressBound() — two batches — stays at 24 MiB, so that a caller who allocates the bound for EVERY
+//     input piece (compressYieldImmediately, Conduit.hsc:385-400) is served from the allocator's heap instead of a fresh
+//     mapping per call: 4.9 GB/s instead of 2.3.
+const char* batch_env() { const char* e = getenv("B2LZ4_BATCH_MB"); return (e && *e) ? e : nullptr; }   // empty = unset
+size_t batch_mb(long dflt) {
+    const char* e = batch_env();
+    long mb = e ? atol(e) : dflt;
+    if (mb < 4) mb = 4;
+    if (mb > 2048) mb = 2048;
+    return ((size_t)mb << 20) & ~(((size_t)4 << 20) - 1);
 }
+size_t batch_bytes() { static size_t v = 0; if (!v) v = batch_mb(32); return v; }
+size_t cbatch_bytes() { static size_t v = 0; if (!v) v = batch_mb(12); return v; }
 int device_index() { const char* e = getenv("B2LZ4_DEVICE"); return e ? atoi(e) : 0; }
 // B2LZ4_DEVICES=0,1,2,3: the batches of this stream shard across these GPUs by block index (b2lz4_set_devices)
 size_t apply_devices(b2lz4_ctx* gpu) {
@@ -174,7 +179,7 @@ size_t LZ4F_compressBound(size_t srcSize, const LZ4F_preferences_t* p) {
     const unsigned id = (unsigned)p->frameInfo.blockSizeID;
     if (id != 0 && (id < 4 || id > 7)) return ec(E_maxBlockSize_invalid);
     const uint32_t bs = block_bytes_of(id);
-    const size_t buffered = p->autoFlush ? 0 : 2 * batch_bytes() - 1;            // one batch on the GPU, one being staged
+    const size_t buffered = p->autoFlush ? 0 : 2 * cbatch_bytes() - 1;            // one batch on the GPU, one being staged
     return blocks_bound(buffered + srcSize, bs, p->frameInfo.blockChecksumFlag != 0) + 8;
 }
 
@@ -230,7 +235,7 @@ static size_t begin_impl(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_prefere
     c->bp.write_index = 0;
     c->bp.block_linked = (literal_mode && c->prefs.frameInfo.blockMode == LZ4F_blockLinked) ? 1u : 0u;
     c->block_size = block_bytes_of(id);
-    c->batch = batch_bytes();
+    c->batch = cbatch_bytes();
     if (!c->gpu) {
         size_t r = b2lz4_create(&c->gpu, device_index(), &c->bp);
         if (b2lz4_is_error(r)) return r;
@@ -467,7 +472,7 @@ size_t header_done(LZ4F_dctx_s* d) {
     // fast is the number of blocks in it, so batches of large blocks are sized by count (16 blocks = 64 MiB of 4 MB blocks;
     // more would cost more in pinned staging than it gains)
     d->batch = std::max(batch_bytes(), std::min<size_t>((size_t)16 * d->info.block_size, (size_t)64 << 20));
-    if (getenv("B2LZ4_BATCH_MB")) d->batch = batch_bytes();
+    if (batch_env()) d->batch = batch_bytes();
     return 0;
 }
 

@@ -5,7 +5,7 @@ usage: python tools/tier1_speed.py [size_mib] [--only-compress]   (B2LZ4_BATCH_M
 import ctypes as C, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
-os.environ.setdefault("B2LZ4_BATCH_MB", "32")                    # the library default (tests/conftest.py lowers it to 8 for coverage)
+os.environ.setdefault("B2LZ4_BATCH_MB", "")                      # empty = the library defaults (tests/conftest.py would lower it to 8 for coverage)
 import conftest
 import importlib
 pkg = importlib.import_module("lz4-frame-conduit_b200"); pkg.load()
@@ -37,8 +37,7 @@ ours.ref_conduit_compress_yi(src, min(n, 64 << 20), comp, cap, 32768)
 cy, ty = t(lambda: ours.ref_conduit_compress_yi(src, n, comp, cap, 32768))
 assert cy < (1 << 62), f"compressYieldImmediately failed with code {(1 << 64) - cy}"
 print(f"b200 LZ4F_* (Tier 1): conduit compressYieldImmediately {n / ty / 1e9:.2f} GB/s, frame {cy} B "
-      f"(batch {os.environ['B2LZ4_BATCH_MB']} MiB, LZ4F_compressBound(32 KB) = {ours.ref_compress_bound(32768) >> 20} MiB)" if hasattr(ours, "ref_compress_bound")
-      else f"b200 LZ4F_* (Tier 1): conduit compressYieldImmediately {n / ty / 1e9:.2f} GB/s, frame {cy} B (batch {os.environ['B2LZ4_BATCH_MB']} MiB)", flush=True)
+      f"(B2LZ4_BATCH_MB={os.environ['B2LZ4_BATCH_MB'] or 'library default'})", flush=True)
 if only_compress:
     sys.exit(0)
 if ref is not None:
