@@ -22,12 +22,25 @@ namespace b2 {
 
 constexpr uint32_t HSIZE = 1u << ENC_HLOG;
 
+#ifndef B2_ENC_MIN_SL
+#define B2_ENC_MIN_SL 0       // smallest probe stride (log2): 1 = every other position even in compressible input (tuning experiment)
+#endif
 #ifndef B2_ENC_WIN
 #define B2_ENC_WIN 0          // 1 = the 128 positions of a stride-1 step take their own bytes from a shared-memory copy of the step window
                               // (measured on B200: 48.9 vs 58.9 GB/s — the kernel is bound by instruction issue, the window costs instructions)
 #endif
 constexpr uint32_t ENC_WIN_WORDS = 44;     // bytes T0 - 4 .. T0 + 127 + 12 + 19 (+ alignment) of a step: what probe, verify and the second measuring pass read at the positions
-size_t find_emit_smem_bytes() { return (size_t)ENC_SMEM_WARPS * HSIZE * sizeof(uint16_t) + (B2_ENC_WIN ? (size_t)ENC_WARPS * ENC_WIN_WORDS * 4u : 0u); }
+#ifndef B2_ENC_COMPACT2B
+#define B2_ENC_COMPACT2B 0    // 1 = the second measuring pass (2b) works on a dense list of the matches that need it, 32 per round, instead of one
+                              // per lane per round at ~30 % lane use (a 128-byte exchange area per warp in shared memory).  Same bytes out; measured
+                              // on B200: 5.4 % fewer instructions, 11 % SLOWER (52.1 vs 58.8 GB/s: the exchange puts two shared-memory round trips
+                              // and a global one on the step's critical path; issue slots 65 % -> 54 %)
+#endif
+constexpr uint32_t ENC_X_WORDS = B2_ENC_COMPACT2B ? 32u : 0u;      // exchange words per warp
+size_t find_emit_smem_bytes() {
+    return (size_t)ENC_SMEM_WARPS * HSIZE * sizeof(uint16_t) + (B2_ENC_WIN ? (size_t)ENC_WARPS * ENC_WIN_WORDS * 4u : 0u)
+         + (size_t)ENC_WARPS * ENC_X_WORDS * 4u;
+}
 
 // the aligned word that holds *pp: in the step window (shared memory) or in global memory
 template <bool WIN> __device__ __forceinline__ const uint32_t* pos_words(const uint8_t* pp, const uint32_t* wwin, uintptr_t gA) {
@@ -159,6 +172,7 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 #else
     uint32_t* const wwin = nullptr;
 #endif
+    [[maybe_unused]] uint32_t* const xch = (uint32_t*)(s_tab + (size_t)ENC_SMEM_WARPS * HSIZE) + (B2_ENC_WIN ? ENC_WARPS * ENC_WIN_WORDS : 0u) + wid * ENC_X_WORDS;
     uint16_t* tab = wid < (uint32_t)ENC_SMEM_WARPS ? s_tab + wid * HSIZE
                   : gtab + ((size_t)blockIdx.x * (ENC_WARPS - ENC_SMEM_WARPS) + (wid - ENC_SMEM_WARPS)) * HSIZE;
 
@@ -267,7 +281,10 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
         while (T0 < limit) {
             // probe stride 1, 2, 4, 8 after 0..3 steps without a hit, 16 after 8, 32 after 16 (the reference's skip
             // acceleration grows the same way: one more byte per 64 failed attempts, lz4.c:895-905)
-            const uint32_t sl = miss < 3u ? miss : miss < 8u ? 3u : miss < 16u ? 4u : 5u;
+            uint32_t sl = miss < 3u ? miss : miss < 8u ? 3u : miss < 16u ? 4u : 5u;
+#if B2_ENC_MIN_SL > 0
+            if (sl < (uint32_t)B2_ENC_MIN_SL) sl = (uint32_t)B2_ENC_MIN_SL;
+#endif
             const uint32_t span = 128u << sl;
             if (lane < 2u && T0 + span + 128u * (lane + 1u) <= usize) prefetch_l1(base + T0 + span + 128u * lane);   // next step's input
             // ---- 0. stride-1 steps (compressible input: almost all of them): the bytes at and around the 128 positions are loaded
@@ -350,8 +367,69 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 }
                 H[k] = __ballot_sync(FULL_MASK, hit);
             }
-            // ---- 2b. matches that filled the first 12 bytes are measured for 16 more, one per lane per round
+            // ---- 2b. matches that filled the first 12 bytes are measured for 16 more
             // (41 % of the matches of log-like data are 12+ bytes, 5 % are 28+; only those reach the warp-wide loop)
+            // `measure16`: bytes 12.. of the match (packed pv) at relative position rl -> pv with its length field updated
+            auto measure16 = [&](uint32_t pv, uint32_t rl) -> uint32_t {
+                const uint32_t room = matchlimit - (d0 + rl);
+                if (room <= 12u) return pv;
+                const uint8_t* cp = base + d0 + (pv & 0x3FFFFFu) + 12u;
+                const uint8_t* pp = base + d0 + rl + 12u;
+                const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
+                const uint32_t* pw = pos_words<WIN>(pp, wwin, gA);
+                const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
+                // only words that hold bytes below matchlimit + 3 are touched (same-word slack only)
+                const uint32_t nw = (room - 12u + 3u) >> 2;                      // words of interest: 1..4+
+                const uint32_t c0 = ldg32(cw), p0 = PW(0);
+                const uint32_t c1 = ldg32(cw + 1), p1 = PW(1);
+                const uint32_t c2 = nw > 1u ? ldg32(cw + 2) : 0u, p2 = nw > 1u ? PW(2) : 0u;
+                const uint32_t c3 = nw > 2u ? ldg32(cw + 3) : 0u, p3 = nw > 2u ? PW(3) : 0u;
+                const uint32_t c4 = (nw > 3u && csh) ? ldg32(cw + 4) : 0u, p4 = (nw > 3u && psh) ? PW(4) : 0u;
+                const uint32_t x0 = __funnelshift_r(c0, c1, csh) ^ __funnelshift_r(p0, p1, psh);
+                const uint32_t x1 = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, psh);
+                const uint32_t x2 = __funnelshift_r(c2, c3, csh) ^ __funnelshift_r(p2, p3, psh);
+                const uint32_t x3 = __funnelshift_r(c3, c4, csh) ^ __funnelshift_r(p3, p4, psh);
+                uint32_t more = x0 ? ((uint32_t)(__ffs(x0) - 1) >> 3)
+                              : x1 ? 4u + ((uint32_t)(__ffs(x1) - 1) >> 3)
+                              : x2 ? 8u + ((uint32_t)(__ffs(x2) - 1) >> 3)
+                              : x3 ? 12u + ((uint32_t)(__ffs(x3) - 1) >> 3) : 16u;
+                if (12u + more > room) more = room - 12u;
+                return (pv & ~(31u << 22)) | ((12u + more) << 22);
+            };
+#if B2_ENC_COMPACT2B
+            {
+                // the matches that need it are numbered across the warp (position order: k major, lane minor) and handled 32 at a
+                // time, one per lane: owner -> exchange word "who owns item i" -> the lane that works on item i fetches the packed
+                // match with shuffles, measures, and hands the result back through the same words
+                bool need[4]; uint32_t idx[4]; uint32_t tot = 0;
+                #pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    need[k] = ((pk[k] >> 22) & 31u) == 12u;
+                    const uint32_t Bk = __ballot_sync(FULL_MASK, need[k]);
+                    idx[k] = tot + (uint32_t)__popc(Bk & ((1u << lane) - 1u));
+                    tot += (uint32_t)__popc(Bk);
+                }
+                const uint32_t rel0 = T0 - d0;
+                for (uint32_t r0 = 0; r0 < tot; r0 += 32u) {
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) if (need[k] && idx[k] - r0 < 32u) xch[idx[k] - r0] = ((uint32_t)k << 5) | lane;
+                    __syncwarp();
+                    const bool valid = r0 + lane < tot;
+                    const uint32_t code = valid ? xch[lane] : 0u;
+                    const uint32_t own = code & 31u, kk = code >> 5;
+                    const uint32_t g0 = __shfl_sync(FULL_MASK, pk[0], own), g1 = __shfl_sync(FULL_MASK, pk[1], own);
+                    const uint32_t g2 = __shfl_sync(FULL_MASK, pk[2], own), g3 = __shfl_sync(FULL_MASK, pk[3], own);
+                    uint32_t pv = kk == 0 ? g0 : kk == 1 ? g1 : kk == 2 ? g2 : g3;
+                    if (valid) pv = measure16(pv, rel0 + ((32u * kk + own) << sl));
+                    __syncwarp();
+                    xch[lane] = pv;
+                    __syncwarp();
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) if (need[k] && idx[k] - r0 < 32u) pk[k] = xch[idx[k] - r0];
+                    __syncwarp();
+                }
+            }
+#else
             {
                 uint32_t todo = 0;
                 #pragma unroll
@@ -362,35 +440,12 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                         todo &= todo - 1u;
                         const uint32_t pv = k == 0 ? pk[0] : k == 1 ? pk[1] : k == 2 ? pk[2] : pk[3];
                         const uint32_t rl = k == 0 ? rel[0] : k == 1 ? rel[1] : k == 2 ? rel[2] : rel[3];
-                        const uint32_t room = matchlimit - (d0 + rl);
-                        if (room > 12u) {
-                            const uint8_t* cp = base + d0 + (pv & 0x3FFFFFu) + 12u;
-                            const uint8_t* pp = base + d0 + rl + 12u;
-                            const uint32_t* cw = (const uint32_t*)((uintptr_t)cp & ~(uintptr_t)3);
-                            const uint32_t* pw = pos_words<WIN>(pp, wwin, gA);
-                            const uint32_t csh = (uint32_t)((uintptr_t)cp & 3u) * 8u, psh = (uint32_t)((uintptr_t)pp & 3u) * 8u;
-                            // only words that hold bytes below matchlimit + 3 are touched (same-word slack only)
-                            const uint32_t nw = (room - 12u + 3u) >> 2;                      // words of interest: 1..4+
-                            const uint32_t c0 = ldg32(cw), p0 = PW(0);
-                            const uint32_t c1 = ldg32(cw + 1), p1 = PW(1);
-                            const uint32_t c2 = nw > 1u ? ldg32(cw + 2) : 0u, p2 = nw > 1u ? PW(2) : 0u;
-                            const uint32_t c3 = nw > 2u ? ldg32(cw + 3) : 0u, p3 = nw > 2u ? PW(3) : 0u;
-                            const uint32_t c4 = (nw > 3u && csh) ? ldg32(cw + 4) : 0u, p4 = (nw > 3u && psh) ? PW(4) : 0u;
-                            const uint32_t x0 = __funnelshift_r(c0, c1, csh) ^ __funnelshift_r(p0, p1, psh);
-                            const uint32_t x1 = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, psh);
-                            const uint32_t x2 = __funnelshift_r(c2, c3, csh) ^ __funnelshift_r(p2, p3, psh);
-                            const uint32_t x3 = __funnelshift_r(c3, c4, csh) ^ __funnelshift_r(p3, p4, psh);
-                            uint32_t more = x0 ? ((uint32_t)(__ffs(x0) - 1) >> 3)
-                                          : x1 ? 4u + ((uint32_t)(__ffs(x1) - 1) >> 3)
-                                          : x2 ? 8u + ((uint32_t)(__ffs(x2) - 1) >> 3)
-                                          : x3 ? 12u + ((uint32_t)(__ffs(x3) - 1) >> 3) : 16u;
-                            if (12u + more > room) more = room - 12u;
-                            const uint32_t nv = (pv & ~(31u << 22)) | ((12u + more) << 22);
-                            if (k == 0) pk[0] = nv; else if (k == 1) pk[1] = nv; else if (k == 2) pk[2] = nv; else pk[3] = nv;
-                        }
+                        const uint32_t nv = measure16(pv, rl);
+                        if (k == 0) pk[0] = nv; else if (k == 1) pk[1] = nv; else if (k == 2) pk[2] = nv; else pk[3] = nv;
                     }
                 }
             }
+#endif
             #undef PW
             };
             if (use_win) verify(std::true_type{}); else verify(std::false_type{});
@@ -529,6 +584,19 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
                 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     if (ok[k] && !((Cm[k] >> lane) & 1u)) TAB_ST(tab + h[k], (uint16_t)rel[k]);
+#if B2_ENC_MIN_SL == 1
+                // stride-2 steps of compressible input: the positions in between are not probed, but they are inserted (a repeat
+                // at an odd distance is then still found, from its even positions), unless both neighbours lie inside a match
+                if (sl == 1u) {
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t cj = (Cm[k] >> lane) & 1u;
+                        const uint32_t cn = lane < 31u ? (Cm[k] >> (lane + 1u)) & 1u : (k < 3 ? Cm[k < 3 ? k + 1 : 3] & 1u : 0u);
+                        const uint32_t p1 = d0 + rel[k] + 1u;
+                        if (p1 < limit && !(cj & cn)) TAB_ST(tab + hash4(ld32u_ro(base + p1)), (uint16_t)(rel[k] + 1u));
+                    }
+                }
+#endif
             }
             __syncwarp();
             T0 += span;
@@ -585,6 +653,7 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
         const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
         const uint32_t ns = (usize + P.sub_size - 1u) / P.sub_size;
         uint32_t carry = 0, off = 0, nc = 0, last_dom = 0xFFFFFFFFu;
+        #pragma unroll 8                                            // (the loads of eight sub-blocks are in flight together: the chain through carry / off is arithmetic only)
         for (uint32_t j = 0; j < ns; ++j) {
             const uint32_t s = b * P.subs_per_block + j;
             const SubOut so = subs[s];
@@ -681,7 +750,9 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
 }
 
 // ------------------------------------------------------------------------------------------------
-// gather: one CTA per sub-block copies its bytes to their final place in the frame.
+// gather: the sub-blocks' bytes go to their final place in the frame.  A CTA takes 8 consecutive sub-blocks at a time: one
+// WARP per compressed sub-block (a few KB each: eight of them in flight per CTA hide the look-ups in front of every copy),
+// the whole CTA for sub-blocks of stored blocks (16 KB of raw input each).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 gather_kernel(const uint8_t* __restrict__ src, EncParams P, const uint8_t* __restrict__ scratch,
@@ -690,35 +761,44 @@ gather_kernel(const uint8_t* __restrict__ src, EncParams P, const uint8_t* __res
               const EncodeResult* __restrict__ res)
 {
     if (res->err != OK) return;
-    const uint32_t tid = threadIdx.x, nt = blockDim.x;
-    for (uint32_t s = blockIdx.x; s < P.n_subs; s += gridDim.x) {
-        const uint32_t blk = s / P.subs_per_block, j = s - blk * P.subs_per_block;
-        const BlockPlace bp = bplaces[blk];
-        const uint64_t blk_start = (uint64_t)blk * P.block_size;
-        const uint32_t b0 = j * P.sub_size;
-        const uint32_t b1 = (b0 + P.sub_size < bp.usize) ? b0 + P.sub_size : bp.usize;
-        uint8_t* data = dst + bp.frame_off + 4;
-        if (j == 0 && tid == 0) st_le32(dst + bp.frame_off, bp.csize | (bp.stored << 31));
-        if (bp.stored) {
-            group_copy(data + b0, src + blk_start + b0, b1 - b0, tid, nt);
-            continue;
+    const uint32_t tid = threadIdx.x, nt = blockDim.x, lane = tid & 31u, wid = tid >> 5, nw = nt >> 5;
+    for (uint32_t g = blockIdx.x * nw; g < P.n_subs; g += gridDim.x * nw) {
+        const uint32_t s = g + wid;
+        if (s < P.n_subs) {
+            const uint32_t blk = s / P.subs_per_block, j = s - blk * P.subs_per_block;
+            const BlockPlace bp = bplaces[blk];
+            if (j == 0 && lane == 0) st_le32(dst + bp.frame_off, bp.csize | (bp.stored << 31));
+            const SubOut so = subs[s];
+            if (!bp.stored && so.emitted) {
+                const uint64_t blk_start = (uint64_t)blk * P.block_size;
+                const uint32_t b0 = j * P.sub_size;
+                const SubPlace sp = places[s];
+                const uint8_t* sc = scratch + (uint64_t)s * P.scratch_stride;
+                uint8_t* out = dst + bp.frame_off + 4 + sp.dst_rel;
+                if (sp.carry_in == 0) group_copy(out, sc, so.out_len, lane, 32);
+                else {
+                    // re-encode the first token with the literals carried in from the previous sub-block(s)
+                    const uint32_t ll2 = so.first_ll + sp.carry_in;
+                    if (lane == 0) out[0] = (uint8_t)(((ll2 < 15u ? ll2 : 15u) << 4) | (sc[0] & 15u));
+                    if (ll2 >= 15u) {
+                        uint32_t r = ll2 - 15u, n255 = r / 255u;
+                        for (uint32_t i = lane; i < n255; i += 32u) out[1 + i] = 255;
+                        if (lane == 0) out[1 + n255] = (uint8_t)(r - n255 * 255u);
+                    }
+                    group_copy(out + sp.new_hdr, src + blk_start + b0 - sp.carry_in, sp.carry_in, lane, 32);
+                    group_copy(out + sp.new_hdr + sp.carry_in, sc + so.first_hdr, so.out_len - so.first_hdr, lane, 32);
+                }
+            }
         }
-        const SubOut so = subs[s];
-        if (!so.emitted) continue;
-        const SubPlace sp = places[s];
-        const uint8_t* sc = scratch + (uint64_t)s * P.scratch_stride;
-        uint8_t* out = data + sp.dst_rel;
-        if (sp.carry_in == 0) { group_copy(out, sc, so.out_len, tid, nt); continue; }
-        // re-encode the first token with the literals carried in from the previous sub-block(s)
-        const uint32_t ll2 = so.first_ll + sp.carry_in;
-        if (tid == 0) out[0] = (uint8_t)(((ll2 < 15u ? ll2 : 15u) << 4) | (sc[0] & 15u));
-        if (ll2 >= 15u) {
-            uint32_t r = ll2 - 15u, n255 = r / 255u;
-            for (uint32_t i = tid; i < n255; i += nt) out[1 + i] = 255;
-            if (tid == 0) out[1 + n255] = (uint8_t)(r - n255 * 255u);
+        for (uint32_t q = 0; q < nw && g + q < P.n_subs; ++q) {            // stored blocks: raw input, copied by the whole CTA
+            const uint32_t s2 = g + q, blk = s2 / P.subs_per_block, j = s2 - blk * P.subs_per_block;
+            const BlockPlace bp = bplaces[blk];
+            if (!bp.stored) continue;
+            const uint32_t b0 = j * P.sub_size;
+            if (b0 >= bp.usize) continue;
+            const uint32_t b1 = (b0 + P.sub_size < bp.usize) ? b0 + P.sub_size : bp.usize;
+            group_copy(dst + bp.frame_off + 4 + b0, src + (uint64_t)blk * P.block_size + b0, b1 - b0, tid, nt);
         }
-        group_copy(out + sp.new_hdr, src + blk_start + b0 - sp.carry_in, sp.carry_in, tid, nt);
-        group_copy(out + sp.new_hdr + sp.carry_in, sc + so.first_hdr, so.out_len - so.first_hdr, tid, nt);
     }
 }
 
