@@ -146,7 +146,7 @@ struct SubPlace {             // written by the layout kernel
     uint32_t dst_rel;         // offset of this sub-block's bytes inside the block's compressed data
     uint32_t carry_in;        // literals inherited from the previous sub-block(s)
     uint32_t new_hdr;         // size of the re-encoded first token + length bytes
-    uint32_t size;            // final bytes of this sub-block inside the block
+    uint32_t size;            // rank + 1 of this sub-block among the decoder entry points of its block (first emitting unit of a match domain), else 0
 };
 
 struct BlockPlace {

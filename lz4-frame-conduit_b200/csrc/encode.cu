@@ -627,62 +627,128 @@ find_emit_kernel(const uint8_t* __restrict__ src, EncParams P, uint8_t* __restri
 }
 
 // ------------------------------------------------------------------------------------------------
-// layout: per-block stitch sizes, stored decision, frame offsets (scan), header / EndMark / index.
-// One CTA of LAYOUT_THREADS threads — no more than one match-finder CTA, so that it can start in any slot a retiring
-// match-finder CTA of ANOTHER chunk frees (the host-buffer pipeline keeps several chunks in flight on different streams).
+// layout, part 1: the sub-blocks of every block are stitched — one WARP per block, a lane per sub-block (32 at a time), the
+// serial rules "literals left over by a sub-block that emitted nothing (or by a tail) are carried into the next one that
+// emits; the first emitting unit of every match domain is a decoder entry point" written as warp scans:
+//   carry   segmented sum of the tails, restarting behind every sub-block that emitted
+//   dst_rel prefix sum of the final sizes (which depend on the carry through the re-encoded first token)
+//   entry   segmented OR over the units of a domain -> first emitting unit, ranked by a ballot
+// (the previous version walked the 256 sub-blocks of a 4 MB block with one thread: 485 us per GiB, 2.7 % of the encoder)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(LAYOUT_THREADS)
-layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict__ places,
-              BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst, uint64_t dst_cap,
-              EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket, uint8_t* __restrict__ idx_frag)
+__global__ void __launch_bounds__(256)
+layout_blocks_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict__ places, BlockPlace* __restrict__ bplaces)
 {
-    constexpr uint32_t NT = LAYOUT_THREADS;
-    B2_SHARED_ARRAY(uint64_t, part_bytes, NT);
-    B2_SHARED_ARRAY(uint32_t, part_chain, NT);
-    B2_SHARED_VAR(EncodeResult, s_res);
-    const uint32_t tid = threadIdx.x;
-    const uint32_t nb = P.n_blocks;
-    const uint32_t bc = P.block_checksum ? 4u : 0u;
-    const uint32_t per = (nb + NT - 1u) / NT;
-    const uint32_t b0 = tid * per < nb ? tid * per : nb, b1 = (b0 + per < nb) ? b0 + per : nb;
-    if (tid == 0) *ticket = 0;
-
-    uint64_t bytes = 0; uint32_t nchain = 0;
-    for (uint32_t b = b0; b < b1; ++b) {
+    const uint32_t lane = lane_id();
+    const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t b = gw; b < P.n_blocks; b += nwarps) {
         const uint64_t blk_start = (uint64_t)b * P.block_size;
         const uint32_t usize = (uint32_t)((P.n - blk_start) < P.block_size ? (P.n - blk_start) : P.block_size);
         const uint32_t ns = (usize + P.sub_size - 1u) / P.sub_size;
-        uint32_t carry = 0, off = 0, nc = 0, last_dom = 0xFFFFFFFFu;
-        #pragma unroll 8                                            // (the loads of eight sub-blocks are in flight together: the chain through carry / off is arithmetic only)
-        for (uint32_t j = 0; j < ns; ++j) {
+        uint32_t carry_run = 0, off_run = 0, nc_run = 0, dom_any_run = 0;
+        for (uint32_t j0 = 0; j0 < ns; j0 += 32u) {
+            const uint32_t j = j0 + lane;
+            const bool valid = j < ns;
             const uint32_t s = b * P.subs_per_block + j;
-            const SubOut so = subs[s];
-            SubPlace sp; sp.dst_rel = off; sp.carry_in = carry; sp.new_hdr = 0; sp.size = 0;
-            if (so.emitted) {
-                uint32_t ll2 = so.first_ll + carry;
-                sp.new_hdr = 1u + len_bytes(ll2);
-                sp.size = so.out_len - so.first_hdr + sp.new_hdr + carry;
-                off += sp.size; carry = so.tail;
-                if (j / P.dom_units != last_dom) { ++nc; last_dom = j / P.dom_units; }   // a decoder entry point per domain
-            } else carry += so.tail;
-            places[s] = sp;
+            SubOut so{};
+            if (valid) so = subs[s];
+            const bool e = valid && so.emitted != 0u;
+            // carry behind sub-block j: its tail if it emitted, else the carry behind j - 1 plus its tail
+            uint32_t v = valid ? so.tail : 0u, f = e ? 1u : 0u;
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t pv = __shfl_up_sync(FULL_MASK, v, d), pf = __shfl_up_sync(FULL_MASK, f, d);
+                if ((int)lane >= d) { if (!f) v += pv; f |= pf; }
+            }
+            const uint32_t c_incl = f ? v : v + carry_run;
+            uint32_t c_in = __shfl_up_sync(FULL_MASK, c_incl, 1);
+            if (lane == 0) c_in = carry_run;
+            uint32_t size = 0, new_hdr = 0;
+            if (e) { new_hdr = 1u + len_bytes(so.first_ll + c_in); size = so.out_len - so.first_hdr + new_hdr + c_in; }
+            uint32_t x = size;
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(FULL_MASK, x, d); if ((int)lane >= d) x += y; }
+            // has a unit of j's domain emitted before j?
+            const bool dstart = (j % P.dom_units) == 0u;
+            uint32_t a = e ? 1u : 0u, g = dstart ? 1u : 0u;
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t pa = __shfl_up_sync(FULL_MASK, a, d), pg = __shfl_up_sync(FULL_MASK, g, d);
+                if ((int)lane >= d) { if (!g) a |= pa; g |= pg; }
+            }
+            const uint32_t any_incl = g ? a : (a | dom_any_run);
+            uint32_t any_excl = __shfl_up_sync(FULL_MASK, any_incl, 1);
+            if (lane == 0) any_excl = dom_any_run;
+            if (dstart) any_excl = 0u;
+            const bool is_first = e && !any_excl;
+            const uint32_t fb = __ballot_sync(FULL_MASK, is_first);
+            if (valid) {
+                SubPlace sp; sp.dst_rel = off_run + x - size; sp.carry_in = c_in; sp.new_hdr = new_hdr;
+                sp.size = is_first ? nc_run + (uint32_t)__popc(fb & ((1u << lane) - 1u)) + 1u : 0u;   // rank of the entry point + 1
+                places[s] = sp;
+            }
+            carry_run = __shfl_sync(FULL_MASK, c_incl, 31); off_run += __shfl_sync(FULL_MASK, x, 31);
+            dom_any_run = __shfl_sync(FULL_MASK, any_incl, 31); nc_run += (uint32_t)__popc(fb);
         }
-        BlockPlace bp; bp.frame_off = 0; bp.usize = usize; bp.first_chain = 0; bp.pad = 0;
-        bp.stored = (off >= usize) ? 1u : 0u;                        // lz4frame.c:746-752
-        bp.csize = bp.stored ? usize : off;
-        bp.n_chain = bp.stored ? 1u : nc;
-        bplaces[b] = bp;
-        bytes += 4ull + bp.csize + bc; nchain += bp.n_chain;
+        if (lane == 0) {
+            BlockPlace bp; bp.frame_off = 0; bp.usize = usize; bp.first_chain = 0; bp.pad = 0;
+            bp.stored = (off_run >= usize) ? 1u : 0u;                    // lz4frame.c:746-752
+            bp.csize = bp.stored ? usize : off_run;
+            bp.n_chain = bp.stored ? 1u : nc_run;
+            bplaces[b] = bp;
+        }
     }
-    part_bytes[tid] = bytes; part_chain[tid] = nchain;
-    __syncthreads();
-    if (tid == 0) {
-        const uint32_t hs = P.write_header ? (7u + (P.desc.has_content_size ? 8u : 0u) + (P.desc.has_dict_id ? 4u : 0u)) : 0u;
-        uint64_t run = hs; uint32_t rc = 0;
-        for (uint32_t i = 0; i < NT; ++i) {
-            uint64_t t = part_bytes[i]; uint32_t c = part_chain[i];
-            part_bytes[i] = run; part_chain[i] = rc; run += t; rc += c;
+}
+
+// ------------------------------------------------------------------------------------------------
+// layout, part 2: frame offsets of the blocks (scan), header / EndMark / index head and block entries.
+// One CTA of LAYOUT_THREADS threads — no more than one match-finder CTA, so that it can start in any slot a retiring
+// match-finder CTA of ANOTHER chunk frees (the host-buffer pipeline keeps several chunks in flight on different streams).
+// Blocks are taken LAYOUT_THREADS at a time, thread t the t-th of them (coalesced), with a CTA-wide scan per round.
+// The index entries of the decoder entry points are written by gather_kernel, which visits every sub-block anyway.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(LAYOUT_THREADS)
+layout_kernel(EncParams P, BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst, uint64_t dst_cap,
+              EncodeResult* __restrict__ res, uint32_t* __restrict__ ticket, uint8_t* __restrict__ idx_frag)
+{
+    constexpr uint32_t NT = LAYOUT_THREADS, NW = NT / 32u;
+    B2_SHARED_ARRAY(uint64_t, w_bytes, NW);
+    B2_SHARED_ARRAY(uint32_t, w_chain, NW);
+    B2_SHARED_VAR(EncodeResult, s_res);
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const uint32_t nb = P.n_blocks;
+    const uint32_t bc = P.block_checksum ? 4u : 0u;
+    if (tid == 0) *ticket = 0;
+    const uint32_t hs = P.write_header ? (7u + (P.desc.has_content_size ? 8u : 0u) + (P.desc.has_dict_id ? 4u : 0u)) : 0u;
+    uint64_t run = hs; uint32_t rc = 0;                              // totals of the rounds so far (uniform)
+    for (uint32_t r0 = 0; r0 < nb; r0 += NT) {
+        const uint32_t b = r0 + tid;
+        BlockPlace bp{};
+        if (b < nb) bp = bplaces[b];
+        const uint64_t my_bytes = b < nb ? 4ull + bp.csize + bc : 0ull;
+        const uint32_t my_chain = b < nb ? bp.n_chain : 0u;
+        uint64_t xb = my_bytes; uint32_t xc = my_chain;
+        #pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint64_t yb = __shfl_up_sync(FULL_MASK, xb, d); const uint32_t yc = __shfl_up_sync(FULL_MASK, xc, d);
+            if ((int)lane >= d) { xb += yb; xc += yc; }
         }
+        if (lane == 31u) { w_bytes[wid] = xb; w_chain[wid] = xc; }
+        __syncthreads();
+        uint64_t pre_b = 0, tot_b = 0; uint32_t pre_c = 0, tot_c = 0;
+        #pragma unroll
+        for (uint32_t w = 0; w < NW; ++w) {
+            const uint64_t wb = w_bytes[w]; const uint32_t wc = w_chain[w];
+            if (w < wid) { pre_b += wb; pre_c += wc; }
+            tot_b += wb; tot_c += wc;
+        }
+        __syncthreads();
+        if (b < nb) {
+            bp.frame_off = run + pre_b + xb - my_bytes; bp.first_chain = rc + pre_c + xc - my_chain;
+            bplaces[b] = bp;
+        }
+        run += tot_b; rc += tot_c;
+    }
+    if (tid == 0) {
         EncodeResult r{};
         r.n_blocks = nb; r.n_chains = rc;
         r.blocks_len = run - hs;
@@ -717,35 +783,17 @@ layout_kernel(EncParams P, const SubOut* __restrict__ subs, SubPlace* __restrict
     }
     __syncthreads();
     if (s_res.err != OK) return;
-    uint64_t run = part_bytes[tid]; uint32_t rc = part_chain[tid];
     // index entries go into the frame's own index (one-shot call) or, when the frame is produced in chunks, into a
     // fragment buffer [nb x IndexBlock][n_chains x IndexChain] that the host rebases and concatenates
     uint8_t* ib = s_res.index_off ? dst + s_res.index_off + 8 + sizeof(IndexHead) : idx_frag;
-    uint8_t* ic = ib ? ib + (uint64_t)nb * sizeof(IndexBlock) : nullptr;
-    for (uint32_t b = b0; b < b1; ++b) {
-        BlockPlace bp = bplaces[b];
-        bp.frame_off = run; bp.first_chain = rc;
-        bplaces[b] = bp;
-        if (ib) {
-            uint8_t* e = ib + (uint64_t)b * sizeof(IndexBlock);
-            st_le32(e, bp.csize | (bp.stored << 31)); st_le32(e + 4, bp.usize);
-            st_le32(e + 8, rc); st_le32(e + 12, bp.n_chain);
-            uint8_t* ce = ic + (uint64_t)rc * sizeof(IndexChain);
-            if (bp.stored) { st_le32(ce, 0u); st_le32(ce + 4, 0u); }
-            else {
-                const uint32_t ns = (bp.usize + P.sub_size - 1u) / P.sub_size;
-                uint32_t last_dom = 0xFFFFFFFFu;
-                for (uint32_t j = 0; j < ns; ++j) {
-                    const uint32_t s = b * P.subs_per_block + j;
-                    if (j / P.dom_units == last_dom || !subs[s].emitted) continue;     // first emitting unit of every domain
-                    last_dom = j / P.dom_units;
-                    const SubPlace sp = places[s];
-                    st_le32(ce, sp.dst_rel); st_le32(ce + 4, j * P.sub_size - sp.carry_in);
-                    ce += sizeof(IndexChain);
-                }
-            }
-        }
-        run += 4ull + bp.csize + bc; rc += bp.n_chain;
+    if (!ib) return;
+    uint8_t* ic = ib + (uint64_t)nb * sizeof(IndexBlock);
+    for (uint32_t b = tid; b < nb; b += NT) {
+        const BlockPlace bp = bplaces[b];
+        uint8_t* e = ib + (uint64_t)b * sizeof(IndexBlock);
+        st_le32(e, bp.csize | (bp.stored << 31)); st_le32(e + 4, bp.usize);
+        st_le32(e + 8, bp.first_chain); st_le32(e + 12, bp.n_chain);
+        if (bp.stored) { uint8_t* ce = ic + (uint64_t)bp.first_chain * sizeof(IndexChain); st_le32(ce, 0u); st_le32(ce + 4, 0u); }
     }
 }
 
@@ -758,10 +806,14 @@ __global__ void __launch_bounds__(256)
 gather_kernel(const uint8_t* __restrict__ src, EncParams P, const uint8_t* __restrict__ scratch,
               const SubOut* __restrict__ subs, const SubPlace* __restrict__ places,
               const BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst,
-              const EncodeResult* __restrict__ res)
+              const EncodeResult* __restrict__ res, uint8_t* __restrict__ idx_frag)
 {
     if (res->err != OK) return;
     const uint32_t tid = threadIdx.x, nt = blockDim.x, lane = tid & 31u, wid = tid >> 5, nw = nt >> 5;
+    // index entries of the decoder entry points (layout_kernel wrote the head and the block entries)
+    const uint64_t index_off = res->index_off;
+    uint8_t* const ib = index_off ? dst + index_off + 8 + sizeof(IndexHead) : idx_frag;
+    uint8_t* const ic = ib ? ib + (uint64_t)P.n_blocks * sizeof(IndexBlock) : nullptr;
     for (uint32_t g = blockIdx.x * nw; g < P.n_subs; g += gridDim.x * nw) {
         const uint32_t s = g + wid;
         if (s < P.n_subs) {
@@ -775,6 +827,10 @@ gather_kernel(const uint8_t* __restrict__ src, EncParams P, const uint8_t* __res
                 const SubPlace sp = places[s];
                 const uint8_t* sc = scratch + (uint64_t)s * P.scratch_stride;
                 uint8_t* out = dst + bp.frame_off + 4 + sp.dst_rel;
+                if (ic && sp.size && lane == 0) {                            // first emitting unit of its domain: (token offset, output offset)
+                    uint8_t* ce = ic + (uint64_t)(bp.first_chain + sp.size - 1u) * sizeof(IndexChain);
+                    st_le32(ce, sp.dst_rel); st_le32(ce + 4, b0 - sp.carry_in);
+                }
                 if (sp.carry_in == 0) group_copy(out, sc, so.out_len, lane, 32);
                 else {
                     // re-encode the first token with the literals carried in from the previous sub-block(s)

@@ -368,15 +368,19 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
         ++launches;
     }
     CU(cudaEventRecord(ctx->ev[1], ctx->st));
-    B2_LAUNCH(layout_kernel, 1, LAYOUT_THREADS, 0, ctx->st, P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p,
-                                           (BlockPlace*)ctx->bplaces.p, d_dst, cap, &ds->eres, &ds->ticket_enc,
-                                           (flags & CL_INDEX_FRAGMENT) ? (uint8_t*)ctx->idx_frag.p : nullptr);
+    uint8_t* const frag = (flags & CL_INDEX_FRAGMENT) ? (uint8_t*)ctx->idx_frag.p : nullptr;
+    if (P.n_blocks) {                             // a warp per block stitches its sub-blocks
+        B2_LAUNCH(layout_blocks_kernel, std::min<uint32_t>((P.n_blocks + 7u) / 8u, (uint32_t)ctx->sm_count * 4u), 256, 0, ctx->st,
+                  P, (const SubOut*)ctx->subs.p, (SubPlace*)ctx->places.p, (BlockPlace*)ctx->bplaces.p);
+        ++launches;
+    }
+    B2_LAUNCH(layout_kernel, 1, LAYOUT_THREADS, 0, ctx->st, P, (BlockPlace*)ctx->bplaces.p, d_dst, cap, &ds->eres, &ds->ticket_enc, frag);
     ++launches;
     if (P.n_subs) {
         uint32_t grid = std::min<uint32_t>(P.n_subs, (uint32_t)ctx->sm_count * 8u);
         B2_LAUNCH(gather_kernel, grid, 256, 0, ctx->st, d_src, P, (const uint8_t*)ctx->scratch.p, (const SubOut*)ctx->subs.p,
                                                  (const SubPlace*)ctx->places.p, (const BlockPlace*)ctx->bplaces.p,
-                                                 d_dst, &ds->eres);
+                                                 d_dst, &ds->eres, frag);
         ++launches;
         if (P.block_checksum) {
             B2_LAUNCH(block_checksums_kernel, (P.n_blocks + 127) / 128, 128, 0, ctx->st, P, (const BlockPlace*)ctx->bplaces.p,

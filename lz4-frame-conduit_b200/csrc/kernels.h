@@ -70,11 +70,12 @@ __global__ void df_finalize_kernel(const FrameIndex* fi, const uint32_t* block_c
 // ---- encode
 __global__ void find_emit_kernel(const uint8_t* src, EncParams P, uint8_t* scratch, SubOut* subs, uint32_t* ticket, uint16_t* gtab);
 size_t find_emit_gtab_bytes(uint32_t grid);
-__global__ void layout_kernel(EncParams P, const SubOut* subs, SubPlace* places, BlockPlace* bplaces,
+__global__ void layout_blocks_kernel(EncParams P, const SubOut* subs, SubPlace* places, BlockPlace* bplaces);
+__global__ void layout_kernel(EncParams P, BlockPlace* bplaces,
                               uint8_t* dst, uint64_t dst_cap, EncodeResult* res, uint32_t* ticket, uint8_t* idx_frag);
 __global__ void gather_kernel(const uint8_t* src, EncParams P, const uint8_t* scratch, const SubOut* subs,
                               const SubPlace* places, const BlockPlace* bplaces, uint8_t* dst,
-                              const EncodeResult* res);
+                              const EncodeResult* res, uint8_t* idx_frag);
 __global__ void block_checksums_kernel(EncParams P, const BlockPlace* bplaces, uint8_t* dst, const EncodeResult* res);
 
 // ---- XXH32
