@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <chrono>
 #include <future>
+#include <string>
 #include <mutex>
 #include <vector>
 #include <stdio.h>
@@ -76,7 +77,7 @@ struct Span { double& acc; double t0; explicit Span(double& a) : acc(a), t0(trac
 // erratic under virtualisation: staging buffers of finished contexts are kept in a small process-wide pool and handed to
 // the next context instead of going back to the driver (a program that runs one conduit after the other pins once).
 struct PinnedPool {
-    static constexpr int SLOTS = 12;
+    static constexpr int SLOTS = 32;
     static constexpr size_t MAX_TOTAL = (size_t)768 << 20;
     std::mutex mu; uint8_t* p[SLOTS] = {}; size_t cap[SLOTS] = {}; size_t total = 0;
     uint8_t* get(size_t n, size_t* got) {                      // smallest pooled buffer that fits without wasting more than 4x
@@ -87,11 +88,25 @@ struct PinnedPool {
         uint8_t* q = p[best]; *got = cap[best]; total -= cap[best]; p[best] = nullptr; cap[best] = 0;
         return q;
     }
+    // keeps the buffer if there is room; large buffers are the expensive ones to pin again, so when the pool is full the
+    // smallest ones give way to a larger newcomer (they are handed back to the driver)
     bool put(uint8_t* q, size_t n) {
-        std::lock_guard<std::mutex> g(mu);
-        if (total + n > MAX_TOTAL) return false;
-        for (int i = 0; i < SLOTS; ++i) if (!p[i]) { p[i] = q; cap[i] = n; total += n; return true; }
-        return false;
+        uint8_t* drop[SLOTS]; int nd = 0; bool kept = false;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            if (n <= MAX_TOTAL) for (;;) {
+                int slot = -1, small = -1;
+                for (int i = 0; i < SLOTS; ++i) {
+                    if (!p[i]) { if (slot < 0) slot = i; }
+                    else if (small < 0 || cap[i] < cap[small]) small = i;
+                }
+                if (slot >= 0 && total + n <= MAX_TOTAL) { p[slot] = q; cap[slot] = n; total += n; kept = true; break; }
+                if (small < 0 || cap[small] >= n) break;          // nothing smaller to evict
+                drop[nd++] = p[small]; total -= cap[small]; p[small] = nullptr; cap[small] = 0;
+            }
+        }
+        for (int i = 0; i < nd; ++i) b2lz4_pinned_free(drop[i]);
+        return kept;
     }
 };
 PinnedPool& pinned_pool() { static PinnedPool* pool = new PinnedPool(); return *pool; }   // never destroyed: outlives CUDA teardown order
@@ -113,6 +128,56 @@ struct Pinned {                              // growable pinned host buffer
     void release() { if (p && !pinned_pool().put(p, cap)) b2lz4_pinned_free(p); p = nullptr; cap = 0; }
 };
 
+// Engine contexts (streams, events, device workspaces, the lanes on other devices) are pooled the same way: creating one
+// costs a dozen cudaMallocs, destroying one as many cudaFrees (device-wide synchronisations; measured between 2 ms and
+// 0.6 s on the pool's virtualised boxes), and a program that runs one conduit after the other would pay both per stream.
+// A context goes back to the pool only if it never saw a CUDA error; it is handed out again for the same device and the
+// same B2LZ4_DEVICES setting, with its preferences and dictionary reset.
+struct EnginePool {
+    static constexpr int SLOTS = 4;
+    std::mutex mu; b2lz4_ctx* c[SLOTS] = {}; int dev[SLOTS] = {}; std::string devs[SLOTS];
+    b2lz4_ctx* get(int device, const std::string& dv) {
+        std::lock_guard<std::mutex> g(mu);
+        for (int i = 0; i < SLOTS; ++i) if (c[i] && dev[i] == device && devs[i] == dv) { b2lz4_ctx* x = c[i]; c[i] = nullptr; return x; }
+        return nullptr;
+    }
+    bool put(b2lz4_ctx* x, int device, const std::string& dv) {
+        std::lock_guard<std::mutex> g(mu);
+        for (int i = 0; i < SLOTS; ++i) if (!c[i]) { c[i] = x; dev[i] = device; devs[i] = dv; return true; }
+        return false;
+    }
+};
+EnginePool& engine_pool() { static EnginePool* pool = new EnginePool(); return *pool; }   // never destroyed (as the pinned pool)
+std::string devices_env() { const char* e = getenv("B2LZ4_DEVICES"); return e ? e : ""; }
+bool engine_pool_on() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_CTX_POOL"); v = (e && *e == '0') ? 0 : 1; } return v == 1; }
+
+struct Engine {                               // an engine context and where it came from
+    b2lz4_ctx* gpu = nullptr; int device = 0; std::string devs;
+    size_t acquire(const b2lz4_prefs* bp) {
+        device = device_index(); devs = devices_env();
+        if (engine_pool_on()) {
+            b2lz4_ctx* x = engine_pool().get(device, devs);
+            if (x) {
+                size_t r = b2lz4_set_prefs(x, bp);
+                if (!b2lz4_is_error(r)) r = b2lz4_set_dict(x, nullptr, 0, 0);
+                if (!b2lz4_is_error(r)) { gpu = x; return 0; }
+                b2lz4_destroy(x);
+            }
+        }
+        size_t r = b2lz4_create(&gpu, device, bp);
+        if (b2lz4_is_error(r)) { gpu = nullptr; return r; }
+        r = apply_devices(gpu);
+        if (b2lz4_is_error(r)) { b2lz4_destroy(gpu); gpu = nullptr; }
+        return r;
+    }
+    void release() {
+        if (!gpu) return;
+        const char* e = b2lz4_last_cuda_error(gpu);
+        if (!(engine_pool_on() && (!e || !*e) && engine_pool().put(gpu, device, devs))) b2lz4_destroy(gpu);
+        gpu = nullptr;
+    }
+};
+
 // LZ4F_default -> 256 KB blocks here, each parsed as ONE independent unit: such a frame needs no side information to be
 // decoded block-parallel (by this library's decoder as by any other), and its ratio on log-like data is 1 % better than
 // the reference's default (linked 64 KB blocks).  4 MB / 1 MB blocks stay available through blockSizeID.
@@ -127,7 +192,7 @@ size_t blocks_bound(size_t n, uint32_t bs, bool bc) { return n + ((n + bs - 1) /
 
 // =========================================================================================== compression
 struct LZ4F_cctx_s {
-    b2lz4_ctx* gpu = nullptr;
+    b2lz4_ctx* gpu = nullptr; Engine eng;
     LZ4F_preferences_t prefs{};
     b2lz4_prefs bp{};
     uint32_t block_size = 0;
@@ -162,7 +227,7 @@ LZ4F_errorCode_t LZ4F_freeCompressionContext(LZ4F_cctx* c) {
     drop_flight(c);
     c->tr.report("cctx");
     const double t0 = trace_on() ? Trace::now() : 0;
-    b2lz4_destroy(c->gpu);
+    c->eng.release(); c->gpu = nullptr;
     const double t1 = trace_on() ? Trace::now() : 0;
     c->in.release(); c->out.release(); c->in2.release();
     if (trace_on()) fprintf(stderr, "[b2lz4 cctx] free: engine context %.3f s, staging %.3f s\n", t1 - t0, Trace::now() - t1);
@@ -237,10 +302,9 @@ static size_t begin_impl(LZ4F_cctx* c, void* dst, size_t cap, const LZ4F_prefere
     c->block_size = block_bytes_of(id);
     c->batch = cbatch_bytes();
     if (!c->gpu) {
-        size_t r = b2lz4_create(&c->gpu, device_index(), &c->bp);
+        size_t r = c->eng.acquire(&c->bp);
         if (b2lz4_is_error(r)) return r;
-        r = apply_devices(c->gpu);
-        if (b2lz4_is_error(r)) return r;
+        c->gpu = c->eng.gpu;
     } else {
         size_t r = b2lz4_set_prefs(c->gpu, &c->bp);
         if (b2lz4_is_error(r)) return r;
@@ -382,7 +446,7 @@ enum DStage { DS_HEADER, DS_SKIP_SIZE, DS_SKIP_DATA, DS_BLOCK_HEADER, DS_BLOCK_D
 }
 
 struct LZ4F_dctx_s {
-    b2lz4_ctx* gpu = nullptr;
+    b2lz4_ctx* gpu = nullptr; Engine eng;
     DStage stage = DS_HEADER;
     uint8_t hdr[HEADER_MAX]; uint32_t hdr_len = 0;          // header / small fixed-size elements being collected
     b2lz4_frame_info info{};
@@ -436,10 +500,9 @@ size_t decode_batch(LZ4F_dctx_s* d) {
     ++d->tr.batches;
     if (!d->gpu) {
         b2lz4_prefs bp; b2lz4_default_prefs(&bp); bp.use_index = 0;
-        r = b2lz4_create(&d->gpu, device_index(), &bp);
+        r = d->eng.acquire(&bp);
         if (b2lz4_is_error(r)) return r;
-        r = apply_devices(d->gpu);
-        if (b2lz4_is_error(r)) return r;
+        d->gpu = d->eng.gpu;
     }
     const size_t cap = (size_t)d->n_complete * d->info.block_size;
     if (!d->out2.ensure(cap + 16, 0, true)) return ec(E_allocation_failed);
@@ -496,7 +559,7 @@ LZ4F_errorCode_t LZ4F_freeDecompressionContext(LZ4F_dctx* d) {
     if (d->flight) { d->job.wait(); (void)d->job.get(); d->flight = false; }
     d->tr.report("dctx");
     const double t0 = trace_on() ? Trace::now() : 0;
-    b2lz4_destroy(d->gpu);
+    d->eng.release(); d->gpu = nullptr;
     const double t1 = trace_on() ? Trace::now() : 0;
     d->in.release(); d->out.release(); d->in2.release(); d->out2.release();
     if (trace_on()) fprintf(stderr, "[b2lz4 dctx] free: engine context %.3f s, staging %.3f s\n", t1 - t0, Trace::now() - t1);
