@@ -126,4 +126,38 @@ __device__ __forceinline__ uint32_t xxh32_thread(const uint8_t* p, uint64_t n) {
     return xxh32_tail(h, p + i, (uint32_t)(n - i));
 }
 
+// ---- XXH32 over [p, p+n) by ONE WARP, seed 0; every lane returns the hash.  The recurrence is serial per accumulator
+// (xxhash.c:269-275), so a warp cannot split the stream — what it can do is load it coalesced: 32 consecutive words (eight
+// 16-byte stripes) per load, every lane multiplying its own word by PRIME2 on the way in, then lanes 0..3 (one accumulator
+// each) pull their eight words over with shuffles.  ~3 x a lone thread on long blocks (block checksums of 4 MB blocks).
+__device__ __forceinline__ uint32_t xxh32_warp(const uint8_t* p, uint64_t n, uint32_t lane) {
+    uint32_t h;
+    uint64_t done = 0;
+    if (n >= 16) {
+        const uint32_t q = lane & 3u;
+        uint32_t acc = q == 0u ? XP1 + XP2 : q == 1u ? XP2 : q == 2u ? 0u : 0u - XP1;
+        const uint64_t nstripes = n >> 4;
+        uint32_t w = (uint64_t)(lane >> 2) < nstripes ? ld32u(p + 4u * lane) * XP2 : 0u;
+        for (uint64_t s0 = 0; s0 < nstripes; s0 += 8) {
+            const uint32_t ns = nstripes - s0 < 8 ? (uint32_t)(nstripes - s0) : 8u;
+            const uint32_t cur = w;
+            const uint64_t s1 = s0 + 8;                                       // the next group is requested before this one is hashed
+            w = (s1 + (lane >> 2) < nstripes) ? ld32u(p + s1 * 16 + 4u * lane) * XP2 : 0u;
+            #pragma unroll
+            for (uint32_t k = 0; k < 8; ++k) {
+                const uint32_t m = __shfl_sync(FULL_MASK, cur, 4u * k + q);
+                if (k < ns) { acc += m; acc = (acc << 13) | (acc >> 19); acc *= XP1; }
+            }
+        }
+        const uint32_t v1 = __shfl_sync(FULL_MASK, acc, 0), v2 = __shfl_sync(FULL_MASK, acc, 1);
+        const uint32_t v3 = __shfl_sync(FULL_MASK, acc, 2), v4 = __shfl_sync(FULL_MASK, acc, 3);
+        h = xxh32_merge(v1, v2, v3, v4);
+        done = nstripes << 4;
+    } else {
+        h = XP5;
+    }
+    h += (uint32_t)n;
+    return xxh32_tail(h, p + done, (uint32_t)(n - done));
+}
+
 }  // namespace b2

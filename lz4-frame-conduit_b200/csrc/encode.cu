@@ -16,6 +16,7 @@
 // (a block is stored raw iff it does not compress to fewer bytes, lz4frame.c:746-752).
 #include <type_traits>
 #include "common.cuh"
+#include "xxh32_cta.cuh"
 #include "kernels.h"
 
 namespace b2 {
@@ -859,16 +860,26 @@ gather_kernel(const uint8_t* __restrict__ src, EncParams P, const uint8_t* __res
 }
 
 // block checksums (lz4frame.c:756-759): XXH32 over the block's stored bytes, appended after them
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 block_checksums_kernel(EncParams P, const BlockPlace* __restrict__ bplaces, uint8_t* __restrict__ dst,
                        const EncodeResult* __restrict__ res)
 {
     if (res->err != OK || !P.block_checksum) return;
-    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    for (; b < P.n_blocks; b += gridDim.x * blockDim.x) {
+    if (P.block_size >= (256u << 10)) {                              // one CTA per block (xxh32_cta.cuh), see verify_block_checksums_kernel
+        B2_SHARED_VAR(XxhCtaShared, S);
+        for (uint32_t b = blockIdx.x; b < P.n_blocks; b += gridDim.x) {
+            const BlockPlace bp = bplaces[b];
+            const uint32_t h = xxh32_cta(S, dst + bp.frame_off + 4, bp.csize);
+            if (threadIdx.x == 0) st_le32(dst + bp.frame_off + 4 + bp.csize, h);
+        }
+        return;
+    }
+    const uint32_t lane = lane_id();                                 // small blocks: one warp per block (xxh32_warp)
+    uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    for (; b < P.n_blocks; b += (gridDim.x * blockDim.x) >> 5) {
         const BlockPlace bp = bplaces[b];
-        uint32_t h = xxh32_thread(dst + bp.frame_off + 4, bp.csize);
-        st_le32(dst + bp.frame_off + 4 + bp.csize, h);
+        const uint32_t h = xxh32_warp(dst + bp.frame_off + 4, bp.csize, lane);
+        if (lane == 0) st_le32(dst + bp.frame_off + 4 + bp.csize, h);
     }
 }
 

@@ -383,7 +383,7 @@ static size_t compress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, ui
                                                  d_dst, &ds->eres, frag);
         ++launches;
         if (P.block_checksum) {
-            B2_LAUNCH(block_checksums_kernel, (P.n_blocks + 127) / 128, 128, 0, ctx->st, P, (const BlockPlace*)ctx->bplaces.p,
+            B2_LAUNCH(block_checksums_kernel, P.block_size >= (256u << 10) ? P.n_blocks : std::min<uint32_t>((P.n_blocks + 7u) / 8u, (uint32_t)ctx->sm_count * 8u), 256, 0, ctx->st, P, (const BlockPlace*)ctx->bplaces.p,
                                                                                  d_dst, &ds->eres);
             ++launches;
         }
@@ -509,7 +509,7 @@ static size_t decompress_launch(b2lz4_ctx* ctx, const uint8_t* d_src, size_t n, 
         B2_LAUNCH(decode_df_kernel, ctx->sm_count * (32u / dfw), dfw * 32u, decode_df_smem_bytes(dfw), ctx->st, d_src, n, d_dst, cap, &ds->fi, bl, W, hist);
         launches += 5;
     }
-    B2_LAUNCH(verify_block_checksums_kernel, std::max(1u, std::min(cap_tables / 128u, 1024u)), 128, 0, ctx->st, 
+    B2_LAUNCH(verify_block_checksums_kernel, std::max(1u, std::min(cap_tables / 8u, (uint32_t)ctx->sm_count * 8u)), 256, 0, ctx->st, 
         d_src, &ds->fi, (const BlockRef*)ctx->blocks.p, &ds->crc_bad);
     CU(cudaEventRecord(ctx->ev[2], ctx->st));
     B2_LAUNCH(decode_finalize_kernel, 1, 256, 0, ctx->st, &ds->fi, (const Piece*)ctx->pieces.p, (const PieceOut*)ctx->outs.p,
