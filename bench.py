@@ -392,6 +392,8 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-foreign", action="store_true", help="no foreign-frame (stock CLI shape) decompression leg")
     ap.add_argument("--skip-sharded", action="store_true", help="no in-process multi-GPU leg (configs 3 and 5)")
+    ap.add_argument("--linked", action="store_true", help="linked blocks (blockMode = linked, SURVEY 8 f4): not the BASELINE configuration")
+    ap.add_argument("--content-checksum", action="store_true", help="frames with the content XXH32 (the stock CLI's default): not the BASELINE configuration")
     ap.add_argument("--block-checksum", action="store_true", help="frames with per-block XXH32 (lz4 -BX): not the BASELINE configuration")
     ap.add_argument("--workload", default="loglike", choices=sorted(WORKLOADS))
     ap.add_argument("--block-id", type=int, default=7, help="frame block size id 4..7 = 64 KB .. 4 MB")
@@ -419,7 +421,8 @@ def main():
     n = args.size_mib << 20
     index = 0 if args.no_index else 1
     codec = pkg.Codec(local, block_size_id=args.block_id, sub_block_log2=min(args.sub_log2, 8 + 2 * args.block_id),
-                      write_index=index, use_index=1, block_checksum=1 if args.block_checksum else 0)
+                      write_index=index, use_index=1, block_checksum=1 if args.block_checksum else 0,
+                      block_linked=1 if args.linked else 0, content_checksum=1 if args.content_checksum else 0)
     workload = WORKLOADS[args.workload]
     block_size = 1 << (8 + 2 * args.block_id)
 

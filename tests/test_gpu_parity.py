@@ -309,6 +309,29 @@ def test_encode_ratio_vs_reference_default(codec, ref, gen, datagen):
         assert ours <= r_ref * 1.02          # north_star tolerance at the stated 4 MB block size
 
 
+def test_block_checksums_of_every_block_size_both_ways(codec, lz4_cli, gen):
+    """blockChecksumFlag (lz4frame.c:756-759, 1604-1611; `lz4 -BX`) at every block size: small blocks are hashed by a warp each,
+    blocks of 256 KB and more by a CTA each (xxh32_cta.cuh).  Our frames must pass `lz4 -d` (which verifies every block), the
+    stock CLI's frames must decode here, and a flipped bit in one must be caught — by the block checksum, not later."""
+    if lz4_cli is None:
+        pytest.skip("oracle/_ref/lz4 not present")
+    d = gen_bytes(gen, "loglike", (9 << 20) + 4321) + os.urandom(70001)
+    for bid in (4, 5, 6, 7):
+        codec.set_prefs(block_size_id=bid, sub_block_log2=16, block_checksum=1, content_checksum=0, content_size=0, write_index=0, use_index=1)
+        fr = codec.compress_bytes(d)
+        r = subprocess.run([lz4_cli, "-d", "-c"], input=fr, capture_output=True)
+        assert r.returncode == 0 and r.stdout == d, (bid, r.stderr[:200])
+        f2 = subprocess.run([lz4_cli, "-c", "-BX", f"-B{bid}", "--no-frame-crc"], input=d, capture_output=True, check=True).stdout
+        out, used = codec.decompress_bytes(f2, max_out=len(d) + 16)
+        assert out == d and used == len(f2), bid
+        bad = bytearray(f2)
+        bad[len(bad) // 3] ^= 0x10
+        with pytest.raises(Exception) as ei:
+            codec.decompress_bytes(bytes(bad), max_out=len(d) + 16)
+        assert "blockChecksum_invalid" in str(ei.value) or "decompressionFailed" in str(ei.value) or "maxBlockSize" in str(ei.value), (bid, str(ei.value))
+    codec.set_prefs(block_size_id=7, block_checksum=0, content_checksum=0, content_size=0, sub_block_log2=18, write_index=1, use_index=1)
+
+
 def test_default_prefs_emit_plain_frames(pkg, lz4_cli, gen):
     """Drop-in default: no trailing index frame, `lz4 -d` on a pipe accepts the output (test/Main.hs:60-85)."""
     with pkg.Codec(0) as c:
