@@ -12,8 +12,10 @@ __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
 #if B2_PTX
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 #else
 __device__ __forceinline__ void prefetch_l1(const void*) {}
+__device__ __forceinline__ void prefetch_l2(const void*) {}
 #endif
 
 // 4 bytes at an arbitrary address, little endian.  Touches only the aligned words that contain them.

@@ -82,6 +82,30 @@ __device__ B2_NOINLINE void walk_blocks_df(const uint8_t* __restrict__ src, uint
     *W.st = st;
 }
 
+// Companion of the decoder-side walk: the walk is a chain of dependent loads, one block header per hop, each a DRAM round trip
+// (0.8 us: 13 ms for the 16 K blocks of a GiB of 64 KB blocks, more than decoding them takes).  A second warp keeps the next
+// megabyte of the stream in L2 ahead of the walker — every line of it, as a header can sit anywhere; the decoding warps read
+// the same lines a moment later — so that a hop costs an L2 hit.  w[1] = walk done, w[4..5] = the walker's position.
+__device__ B2_NOINLINE void walk_prefetch(const uint8_t* __restrict__ src, uint64_t n, volatile uint32_t* w, uint32_t lane)
+{
+    constexpr uint64_t AHEAD = 1ull << 20, ROUND = 64ull << 10;
+    uint64_t pf = 0;
+    for (;;) {
+        uint32_t done = 0, lo = 0, hi = 0;
+        if (lane == 0) { done = w[1]; lo = w[4]; hi = w[5]; }
+        done = __shfl_sync(FULL_MASK, done, 0); lo = __shfl_sync(FULL_MASK, lo, 0); hi = __shfl_sync(FULL_MASK, hi, 0);
+        if (done) break;
+        uint64_t cur = (uint64_t)lo | ((uint64_t)hi << 32);
+        if (cur > n) cur = n;                                   // (a torn read of the two halves: harmless)
+        const uint64_t lim = cur + AHEAD < n ? cur + AHEAD : n;
+        if (pf < cur) pf = cur;
+        if (pf >= lim) { __nanosleep(200); continue; }
+        const uint64_t stop = pf + ROUND < lim ? pf + ROUND : lim;
+        for (uint64_t a = (pf & ~127ull) + 128ull * lane; a < stop; a += 4096ull) prefetch_l2(src + a);
+        pf = stop;
+    }
+}
+
 __device__ B2_NOINLINE void walk_blocks(const uint8_t* __restrict__ src, uint64_t n, uint32_t mode, FrameIndex& s,
                             BlockRef* blocks, uint32_t cap_blocks, Piece* pieces, uint32_t cap_pieces, Chain* chains,
                             uint32_t* stored_list, volatile uint32_t* progress)
@@ -125,6 +149,7 @@ __device__ B2_NOINLINE void walk_blocks(const uint8_t* __restrict__ src, uint64_
         }
         ++nb;
         ip += (uint64_t)cs + bc;
+        if (progress) { progress[4] = (uint32_t)ip; progress[5] = (uint32_t)(ip >> 32); }   // where the prefetching warp should be ahead of
     }
     if (progress) { __threadfence(); *progress = nb < cap_blocks ? nb : cap_blocks; }
     if (err == OK && cc) {
@@ -283,7 +308,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
         if ((mode & SCAN_OVERLAP_WALK) && s.desc.block_independent && !(mode & SCAN_SINGLE_CHAIN)) {
             // the walk is left to the decoder kernel, which runs it next to the decoding warps (walk_blocks below)
             s.walk_pending = 1;
-            walk[0] = 0; walk[1] = 0; walk[2] = 0;
+            walk[0] = 0; walk[1] = 0; walk[2] = 0; walk[4] = s.desc.header_size; walk[5] = 0;
             *fi = s;
             return;
         }
@@ -326,8 +351,10 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* _
     const bool pending = fi->walk_pending != 0;
     const uint32_t block_size = fi->block_size;
     const bool linked = !fi->desc.block_independent;
-    uint32_t walker = 0;
-    if (pending) { if (lane == 0) walker = atomicAdd(walk + 2, 1u) == 0u ? 1u : 0u; walker = __shfl_sync(FULL_MASK, walker, 0); }
+    uint32_t role = 0xFFFFFFFFu;                                     // 0 = walker, 1 = its prefetching companion
+    if (pending) { if (lane == 0) role = atomicAdd(walk + 2, 1u); role = __shfl_sync(FULL_MASK, role, 0); }
+    const uint32_t walker = role == 0u ? 1u : 0u;
+    if (role == 1u) walk_prefetch(src, n_src, (volatile uint32_t*)walk, lane);
     if (walker) {
         if (lane == 0) {
             FrameIndex s = *fi;

@@ -52,7 +52,7 @@ struct Small {                 // small device-side state, mirrored to pinned ho
     EncodeResult eres;
     XxhState xxh;
     uint32_t ticket_dec, ticket_enc, crc_bad, hash_out;
-    uint32_t walk[4];          // decoder-side block walk: chains published so far, done flag, walker ticket
+    uint32_t walk[8];          // decoder-side block walk: chains published so far, done flag, role ticket, -, walker position (lo, hi), -, -
     DfState dfst;              // dataflow decode: tickets, first failure, byte counts
 };
 
