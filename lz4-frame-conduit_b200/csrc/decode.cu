@@ -322,6 +322,9 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
 #include "xxh32_cta.cuh"
 namespace b2 {
 
+#ifndef B2_WALK_NAP_NS
+#define B2_WALK_NAP_NS 300      // waiting for the decoder-side walk: nanoseconds of sleep per block of distance
+#endif
 #ifndef B2_DEC_MINCTAS
 #define B2_DEC_MINCTAS 4      // 8 warps x 4 CTAs: 64 registers per thread, 32 warps per SM
 #endif
@@ -377,9 +380,13 @@ decode_chains_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* _
             if (lane == 0) {
                 volatile uint32_t* w = (volatile uint32_t*)walk;
                 for (;;) {
-                    if (c < w[0]) { ok = 1; break; }
+                    const uint32_t p = w[0];
+                    if (c < p) { ok = 1; break; }
                     if (w[1]) { ok = c < w[0] ? 1u : 0u; break; }
-                    __nanosleep(400);
+                    // thousands of warps wait here when the blocks are small: a warp far from its turn asks rarely (the walker
+                    // needs ~0.7 us per block), so that the polls do not crowd the walker's own loads out of the L2 slice
+                    const uint32_t d = c - p;
+                    __nanosleep(d < 8u ? 300u : d < 160u ? d * B2_WALK_NAP_NS : 160u * B2_WALK_NAP_NS);
                 }
                 __threadfence();
             }
