@@ -461,6 +461,7 @@ struct LZ4F_dctx_s {
     uint64_t total_out = 0;
     bool first = true;
     size_t pre_acked = 0;                                    // input bytes already buffered but reported as unconsumed
+    bool launch_pending = false;                             // a batch of whole blocks is staged and goes to the GPU as soon as no other is in flight
     size_t batch = 0;
     std::vector<uint8_t> dict;                               // LZ4F_decompress_usingDict: last 64 KB of the dictionary of the current frame
     Trace tr;
@@ -472,7 +473,7 @@ void dctx_reset(LZ4F_dctx_s* d) {
     if (d->flight) { d->job.wait(); (void)d->job.get(); d->flight = false; }
     d->stage = DS_HEADER; d->hdr_len = 0; d->in_len = 0; d->complete_end = 0; d->n_complete = 0; d->need = 0;
     d->skip_left = 0; d->out_len = d->out_pos = 0; d->total_out = 0; d->first = true; d->pre_acked = 0;
-    d->check_sum = false; d->stored_sum = 0;
+    d->check_sum = false; d->stored_sum = 0; d->launch_pending = false;
     d->dict.clear();                                             // a dictionary belongs to one frame (LZ4F_decompress_usingDict registers it again)
 }
 
@@ -635,14 +636,23 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
             const size_t k = std::min(dstCap - produced, d->out_len - d->out_pos);
             { Span sp(d->tr.t_out); memcpy(dst + produced, d->out.p + d->out_pos, k); }
             produced += k; d->out_pos += k;
-            if (d->out_pos < d->out_len) break;                                      // destination full
         }
+        const bool dst_full = d->out_pos < d->out_len;
         // `out` is drained: the batch in flight is taken over as soon as it is done, or when nothing else is left to do
-        if (d->flight && (d->stage == DS_DONE || job_done(d))) {
+        if (!dst_full && d->flight && (d->stage == DS_DONE || d->launch_pending || job_done(d))) {
             size_t r = collect(d);
             if (b2lz4_is_error(r)) return fail(r);
             continue;
         }
+        // a staged batch goes to the GPU as soon as no other is in flight — also while the caller is still draining the output
+        // of the one before it (the destination being full does not stop the INPUT side: the GPU then works while the caller copies)
+        if (d->launch_pending && !d->flight) {
+            d->launch_pending = false;
+            size_t r = decode_batch(d);
+            if (b2lz4_is_error(r)) return fail(r);
+            continue;
+        }
+        if (dst_full && d->launch_pending) break;                                   // (a batch is in flight and the next one is staged: only draining helps)
         if (d->stage == DS_DONE) break;
         if (consumed == srcSize) break;
         const size_t avail = srcSize - consumed;
@@ -681,8 +691,7 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
             const uint32_t cs = w & 0x7FFFFFFFu;
             if (cs == 0) {                                                           // EndMark (lz4frame.c:1485-1488)
                 d->in_len -= 4;
-                size_t r = decode_batch(d);
-                if (b2lz4_is_error(r)) return fail(r);
+                d->launch_pending = d->n_complete != 0;                              // what is staged is the frame's last batch
                 d->stage = DS_SUFFIX; d->need = d->info.content_checksum ? 4 : 0; d->hdr_len = 0;
                 if (d->need == 0) d->stage = DS_DONE;                                // size / checksum are checked when all is decoded
                 break;
@@ -701,10 +710,7 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
             d->complete_end = d->in_len; ++d->n_complete;
             d->stage = DS_BLOCK_HEADER; d->need = 4;
             // enough for the GPU: the batch's output bound or its compressed size reached the batch size
-            if ((size_t)(d->n_complete + 1) * d->info.block_size > d->batch || d->complete_end >= d->batch) {
-                size_t r = decode_batch(d);
-                if (b2lz4_is_error(r)) return fail(r);
-            }
+            if ((size_t)(d->n_complete + 1) * d->info.block_size > d->batch || d->complete_end >= d->batch) d->launch_pending = true;
             break;
         }
         case DS_SUFFIX: {                                                            // content checksum (lz4frame.c:1734-1745)
@@ -723,7 +729,7 @@ size_t LZ4F_decompress(LZ4F_dctx* d, void* dstBuffer, size_t* dstSizePtr, const 
         dctx_reset(d);
         return 0;
     }
-    const bool pending = d->out_pos < d->out_len || (d->flight && d->stage == DS_DONE);
+    const bool pending = d->out_pos < d->out_len || ((d->flight || d->launch_pending) && d->stage == DS_DONE);
     if (d->stage == DS_DONE && !pending) {                                           // everything is decoded: the frame's own checks
         if (d->check_sum) {                                                          // content checksum (lz4frame.c:1734-1745)
             uint32_t h = 0x02CC5D05u;                                                // XXH32 of no bytes, seed 0 (frame without blocks)
