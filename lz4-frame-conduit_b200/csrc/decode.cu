@@ -300,7 +300,8 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
     if (tid == 0) {
         // no (usable) index.  Dataflow decode pays where a block is long (few blocks, each one dependent chain for a lone
         // warp): linked frames, 4 MB blocks, legacy frames; many small independent blocks are faster one warp per block
-        if ((mode & SCAN_DF) && ((mode & (SCAN_DF_ALL | SCAN_LEGACY)) || !s.desc.block_independent || s.block_size >= (4u << 20))) {
+        const bool few = (mode & SCAN_DF_FEW) && dst_cap / s.block_size <= (uint64_t)DF_FEW_BLOCKS;
+        if ((mode & SCAN_DF) && ((mode & (SCAN_DF_ALL | SCAN_LEGACY)) || !s.desc.block_independent || s.block_size >= (4u << 20) || few)) {
             walk_blocks_df(src, n, mode, s, blocks, cap_blocks, W);
             *fi = s;
             return;

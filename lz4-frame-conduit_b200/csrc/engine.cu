@@ -441,7 +441,8 @@ size_t b2lz4_compress_device(b2lz4_ctx* ctx, const void* d_src, size_t n, void* 
 // dataflow mode is on unless B2LZ4_DF=0 (then unindexed frames decode one warp per block, linked frames one warp per frame)
 static int df_level() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_DF"); v = !e ? 1 : (*e == '0') ? 0 : (*e == '2') ? 2 : 1; } return v; }
 static bool df_enabled() { return df_level() != 0; }
-static uint32_t df_mode() { return df_level() == 0 ? 0u : df_level() == 2 ? (SCAN_DF | SCAN_DF_ALL) : SCAN_DF; }
+static bool df_few() { static int v = -1; if (v < 0) { const char* e = getenv("B2LZ4_DF_FEW"); v = (e && *e == '0') ? 0 : 1; } return v == 1; }
+static uint32_t df_mode() { return df_level() == 0 ? 0u : df_level() == 2 ? (SCAN_DF | SCAN_DF_ALL) : (SCAN_DF | (df_few() ? SCAN_DF_FEW : 0u)); }
 
 // warps per CTA of decode_df_kernel: B2LZ4_DF_WARPS, else by the size of the call (a guess at the number of units: the
 // host does not know the block size of a device-resident frame)

@@ -38,9 +38,11 @@ constexpr int DF_WARPS = B2_DF_WARPS;            // warps per CTA in df_links_ke
 enum : uint32_t { SCAN_USE_INDEX = 1u, SCAN_SINGLE_CHAIN = 2u, SCAN_BATCH = 4u,
                   SCAN_DF = 32u,              // frames without a usable index may go to the dataflow kernels (decode_df.cu)
                   SCAN_DF_ALL = 64u,          // ... whatever their block size (B2LZ4_DF=2; the exact-layout retry)
+                  SCAN_DF_FEW = 128u,         // ... and calls of few blocks (one warp per block would leave most SMs with one warp or none)
                   SCAN_LEGACY = 8u,
                   SCAN_OVERLAP_WALK = 16u };  // plain independent-block frames: walk the block headers inside the decoder kernel   // blocks of a legacy frame (lz4_Frame_format.md:338-386): 8 MB, always compressed, no flag bit
 constexpr uint32_t LEGACY_BLOCK = 8u << 20;
+constexpr uint32_t DF_FEW_BLOCKS = 256u;     // SCAN_DF_FEW: at most this many blocks fit the destination
 
 // ---- decode
 __global__ void frame_scan_kernel(const uint8_t* src, uint64_t n, uint64_t dst_cap, uint32_t mode,
