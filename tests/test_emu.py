@@ -232,6 +232,27 @@ print('ok')
 """
 
 
+def test_emu_pooled_engine_contexts_carry_nothing_over(emu_replay, oracle, manifest, gen):
+    """Freed LZ4F contexts hand their engine context to a process-wide pool (lz4f_compat.cu: EnginePool); the next LZ4F
+    context gets it back with other preferences.  A dictionary, linked-block history, checksum state or block size of the
+    stream before must not show in the stream after — in either direction."""
+    dic = golden_bytes(manifest["_dict"]["file"])
+    a = gen_bytes(gen, "loglike", 400000, 11)
+    b = gen_bytes(gen, "textlike", 300000, 12) + bytes(50000)
+    cap = 1 << 20
+    for rnd in range(2):
+        with_dict = dict_compress(emu_replay, a, dic, 4, 0, 1, 77)                   # linked blocks + dictionary + content checksum
+        assert dict_decompress(emu_replay, with_dict, dic, len(a) + 64, 5000) == a
+        o = C.create_string_buffer(cap)
+        r = emu_replay.ref_conduit_compress(b, len(b), o, cap, 16384, 0)             # the plain conduit right after: no dictionary, no checksum
+        plain = o.raw[:r]
+        got, used = orc_decode(oracle, plain, len(b) + 64)
+        assert got == b and used == len(plain), rnd
+        got, used = ref_conduit_decode(emu_replay, plain, len(b) + 64, chunk=7001)
+        assert got == b and used == len(plain), rnd
+        assert dict_decompress(emu_replay, with_dict, dic, len(a) + 64) == a        # and the dictionary stream again after the plain one
+
+
 def test_emu_dataflow_forced_for_every_frame(emu):
     """B2LZ4_DF=2: independent small-block frames (normally one warp per block) through the dataflow kernels as well."""
     assert "ok" in _run_with_env({"B2LZ4_DF": "2"}, _GOLDEN_LOOP)
