@@ -1,5 +1,5 @@
 import os, sys, importlib.util, ctypes as C
-ROOT='/root/repo'
+ROOT=os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["B2LZ4_LIB"]=os.path.join(ROOT,"tests/_build/libb200lz4_emu.so"); os.environ["B2_EMU_DEVICES"]="2"
 pkgdir=os.path.join(ROOT,"lz4-frame-conduit_b200")
 spec=importlib.util.spec_from_file_location("b2emu", os.path.join(pkgdir,"__init__.py"), submodule_search_locations=[pkgdir])

@@ -1,5 +1,5 @@
 import os, sys, random, ctypes as C
-ROOT='/root/repo'
+ROOT=os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["B2LZ4_BATCH_MB"]="4"
 lib=C.CDLL(os.path.join(ROOT,"tests/_build/libb200lz4_emu.so"))
 sz=C.c_size_t

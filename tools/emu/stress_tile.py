@@ -1,5 +1,5 @@
 import os, sys, random, importlib.util, ctypes as C
-ROOT='/root/repo'
+ROOT=os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT,'tests'))
 os.environ["B2LZ4_LIB"]=os.path.join(ROOT,"tests/_build/libb200lz4_emu.so")
 pkgdir=os.path.join(ROOT,"lz4-frame-conduit_b200")
