@@ -265,12 +265,14 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
                 ncb == 0 || fc != cnt || (uint64_t)fc + ncb > nc || ((w >> 31) && (ncb != 1 || cs != us))) { s_bad = 1; break; }
             BlockRef br; br.src_off = a + 4; br.csize = cs; br.stored = w >> 31; br.dst_off = d; br.usize = us; br.pad = 0;
             blocks[b] = br;
+            bool bad = false;                                       // (no exit from inside the loop: the loads of the next entries do not wait for this one's checks)
+            #pragma unroll 4
             for (uint32_t k = 0; k < ncb; ++k) {
                 const uint8_t* ce = ic + (uint64_t)(fc + k) * sizeof(IndexChain);
                 uint32_t tok = ld_le32_dev(ce), out = ld_le32_dev(ce + 4);
                 uint32_t tok_n = cs, out_n = us;
                 if (k + 1 < ncb) { tok_n = ld_le32_dev(ce + 8); out_n = ld_le32_dev(ce + 12); }
-                if ((k == 0 && (tok != 0 || out != 0)) || tok >= tok_n || out > out_n || tok_n > cs || out_n > us) { s_bad = 1; break; }
+                if ((k == 0 && (tok != 0 || out != 0)) || tok >= tok_n || out > out_n || tok_n > cs || out_n > us) { bad = true; continue; }
                 Piece pc; pc.src_off = a + 4 + tok; pc.src_len = tok_n - tok;
                 pc.flags = PIECE_EXACT | (br.stored ? (PIECE_STORED | PIECE_BULK) : 0u) | (k + 1 == ncb ? PIECE_ENDS_BLOCK : 0u);
                 if (br.stored) stored_list[atomicAdd(&s_nstored, 1u)] = fc + k;     // copied by copy_stored_kernel
@@ -279,6 +281,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
                 Chain ch; ch.dst_off = d + out; ch.first_piece = fc + k; ch.n_pieces = 1;
                 chains[fc + k] = ch;
             }
+            if (bad) { s_bad = 1; break; }
             a += 4ull + cs + bc; d += us; cnt += ncb;
         }
         __syncthreads();
