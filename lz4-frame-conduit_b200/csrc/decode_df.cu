@@ -314,9 +314,10 @@ struct DfCta {                                  // shared-memory control block o
     unsigned long long ring_hi[DF_RING];        // output end of the ticket in this ring slot
     uint32_t ring_done[DF_RING];                // 1 = done, 2 = done and ran solo (no bits to clear)
     uint32_t lowest, next, lock, unit, t_end, pad;
+    unsigned long long valid_from;              // B2_DF_SMEMWIN: bytes below this buffer offset are not in the data window (a solo ticket wrote them to global memory)
 };
 
-size_t decode_df_smem_bytes(uint32_t warps) { return sizeof(DfCta) + DF_WIN_BYTES / 8u + (size_t)warps * 1568u + 64u; }
+size_t decode_df_smem_bytes(uint32_t warps) { return sizeof(DfCta) + DF_WIN_BYTES / 8u + DF_DATA_BYTES + (size_t)warps * 1568u + 64u; }
 
 // a finished ticket: publish it, then retire every finished ticket at the low end (clear their bits, raise the watermark)
 __device__ __forceinline__ void df_retire(DfCta* C, const DfShared& S, uint32_t t, uint64_t hi, bool solo, uint32_t lane) {
@@ -340,6 +341,12 @@ __device__ __forceinline__ void df_retire(DfCta* C, const DfShared& S, uint32_t 
                 if (lane == 0) { d = ((volatile uint32_t*)C->ring_done)[low % DF_RING]; h = ((volatile unsigned long long*)C->ring_hi)[low % DF_RING]; }
                 d = __shfl_sync(FULL_MASK, d, 0); h = __shfl_sync(FULL_MASK, h, 0);
                 if (!d) break;
+#if B2_DF_SMEMWIN
+                DF_FENCE();
+                if (d == 1u) df_flush(S, F, h, lane);                             // the ticket's bytes leave the data window for global memory, in rows
+                else if (lane == 0) *(volatile unsigned long long*)&C->valid_from = h;   // a solo ticket wrote global memory itself
+                __syncwarp();
+#endif
                 if (d == 1u) df_mark_warp(S, F, h, lane, false);                  // its bits are not needed any more: the watermark says it
                 __syncwarp();
                 if (lane == 0) ((volatile uint32_t*)C->ring_done)[low % DF_RING] = 0u;
@@ -373,12 +380,13 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
     DfCta* const C = (DfCta*)smem;
     uint32_t* const bits = (uint32_t*)(smem + ((sizeof(DfCta) + 15u) & ~(size_t)15u));
     const uint32_t lane = lane_id(), wid = threadIdx.x >> 5;
-    uint8_t* const my_win = (uint8_t*)(bits + DF_WIN_BYTES / 32u) + wid * 1568u;
+    uint8_t* const wdata = (uint8_t*)(bits + DF_WIN_BYTES / 32u);           // (16-byte aligned: everything in front of it is)
+    uint8_t* const my_win = wdata + DF_DATA_BYTES + wid * 1568u;
     for (uint32_t i = lane; i < 5u * 128u; i += 32u) {                       // upper halves of the link tables are identity for good
         const uint32_t t = i >> 7, x = 128u + (i & 127u);
         my_win[272u + 256u * t + x] = (uint8_t)x;
     }
-    DfShared S; S.bits = bits; S.final_below = &C->final_below;
+    DfShared S; S.bits = bits; S.final_below = &C->final_below; S.wdata = wdata; S.gdst = dst; S.wlo = (uint32_t)(uintptr_t)dst & 15u; S.gcap = dst_cap;
     const uint32_t nb = fi->n_blocks, block_size = fi->block_size, nunits = W.st->n_units;
     const bool linked = !fi->desc.block_independent;
     const uint8_t* const src_end = src + n_src;
@@ -402,7 +410,7 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
         for (uint32_t i = threadIdx.x; i < DF_WIN_BYTES / 32u; i += blockDim.x) bits[i] = 0u;
         for (uint32_t i = threadIdx.x; i < DF_RING; i += blockDim.x) C->ring_done[i] = 0u;
         if (threadIdx.x == 0) {
-            C->final_below = br0.dst_off; C->lowest = C->next = W.tk_base[bf]; C->t_end = W.tk_base[bl]; C->lock = 0u;
+            C->final_below = br0.dst_off; C->lowest = C->next = W.tk_base[bf]; C->t_end = W.tk_base[bl]; C->lock = 0u; C->valid_from = br0.dst_off;
         }
         __syncthreads();
         const uint32_t t_end = C->t_end;
@@ -436,7 +444,7 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                 for (;;) {
                     const uint32_t low = *(volatile uint32_t*)&C->lowest;
                     const unsigned long long F = *(volatile unsigned long long*)&C->final_below;
-                    const bool fits = blk_out + out_end <= F + DF_HALF;
+                    const bool fits = blk_out + out_end <= F + DF_HALF && !(B2_DF_SMEMWIN && br.stored);   // (data window: a raw block goes straight to global memory, alone)
                     if (t == low) { solo = fits ? 0u : 1u; break; }
                     if (t - low < DF_RING && fits) break;
                     __nanosleep(nap); nap = nap < 4u * DF_NAP_MAX ? nap * 2u : 4u * DF_NAP_MAX;
@@ -467,7 +475,16 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                 // output of the frame, and of earlier batches in front of the buffer (lz4frame.c:1286-1349)
                 if (linked) { const uint64_t h = blk_out + hist; cu.reach = h > 0x40000000ull ? 0x40000000u : (uint32_t)h; }
                 else cu.reach = 0u;
-                cu.df = S; cu.abs0 = (int64_t)blk_out; cu.solo = solo != 0u; cu.prof_rounds = cu.prof_naps = 0; cu.prof_cyc[0] = cu.prof_cyc[1] = cu.prof_cyc[2] = cu.prof_cyc[3] = 0;
+                cu.df = S; cu.abs0 = (int64_t)blk_out; cu.solo = solo != 0u;
+                {   // what this ticket may read from the data window: not what a solo ticket left out of it, and not what later
+                    // tickets may overwrite while this one runs (they are admitted up to DF_HALF beyond the watermark, which cannot
+                    // pass this ticket's start; everything below that was flushed before this ticket was admitted)
+                    unsigned long long vf = 0;
+                    if (lane == 0) vf = *(volatile unsigned long long*)&C->valid_from;
+                    vf = __shfl_sync(FULL_MASK, vf, 0);
+                    const int64_t lo2 = (int64_t)(blk_out + out_end) - (int64_t)DF_HALF;
+                    cu.df_slo = (int64_t)vf > lo2 ? (int64_t)vf : lo2;
+                } cu.prof_rounds = cu.prof_naps = 0; cu.prof_cyc[0] = cu.prof_cyc[1] = cu.prof_cyc[2] = cu.prof_cyc[3] = 0;
                 for (;;) {
                     e = decode_piece<true>(cu, last_of_block);
                     if (e != DEC_PAUSED) break;
@@ -475,6 +492,11 @@ decode_df_kernel(const uint8_t* __restrict__ src, uint64_t n_src, uint8_t* __res
                     __syncwarp();
                     const int64_t a = (int64_t)blk_out + (int64_t)cu.p_dst - (int64_t)cu.p_off;
                     if (!solo) { uint32_t nap = DF_NAP_MIN; while (!df_ready_warp(S, a, (int64_t)blk_out + cu.p_dst, lane)) { __nanosleep(nap); nap = nap < DF_NAP_MAX ? nap * 2u : DF_NAP_MAX; } DF_FENCE(); }
+                    if (B2_DF_SMEMWIN && !solo) {                             // into the data window: period replication from the final window
+                        const uint32_t di = df_widx(S, (int64_t)blk_out + cu.p_dst);
+                        uint32_t r = lane % cu.p_off; const uint32_t step = 32u % cu.p_off;
+                        for (uint32_t i = lane; i < cu.p_ml; i += 32u) { wdata[(di + i) & DF_DATA_MASK] = df_getb(S, cu.df_slo, a + (int64_t)r); r += step; if (r >= cu.p_off) r -= cu.p_off; }
+                    } else
                     warp_match_overlap(cu.dp + cu.p_dst, cu.p_off, cu.p_ml, lane);
                     if (!solo) { DF_FENCE(); __syncwarp(); df_mark_warp(S, blk_out + cu.p_dst, blk_out + cu.p_dst + cu.p_ml, lane); }
                     __syncwarp();

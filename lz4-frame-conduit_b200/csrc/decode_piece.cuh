@@ -47,6 +47,7 @@ struct Cursor {            // what the warp knows about the piece it is decoding
     uint32_t prof_cyc[4];              // ... cycles: parse, literals, chase, match rounds
     bool solo;             // the piece runs alone (every earlier byte is final, nobody reads the map): no waits, no marks
     uint8_t* tile;         // B2_DEC_TILE bytes of this warp's shared memory (16-byte aligned), unused in dataflow mode
+    int64_t df_slo;        // B2_DF_SMEMWIN: sources at buffer offsets >= this are read from the CTA's data window, lower ones from global memory
 };
 
 // the CTA-scope fence of the dataflow hand-over (tuning builds: -DB2_DF_FENCE=0 none — measurement only, not correct;
@@ -125,6 +126,26 @@ __device__ __forceinline__ void df_mark_warp(const DfShared& S, uint64_t a, uint
         if (w == w1) m &= m1;
         if (set) atomicOr(S.bits + (w & DF_WIN_MASK), m); else atomicAnd(S.bits + (w & DF_WIN_MASK), ~m);
     }
+}
+
+// ---- B2_DF_SMEMWIN: the data window.  Index of buffer offset p; one byte of the unit's output wherever it lives.
+__device__ __forceinline__ uint32_t df_widx(const DfShared& S, int64_t p) { return ((uint32_t)p + S.wlo) & DF_DATA_MASK; }
+__device__ __forceinline__ uint8_t df_getb(const DfShared& S, int64_t slo, int64_t p) {
+    return p >= slo ? S.wdata[df_widx(S, p)] : S.gdst[p];
+}
+// writes the window's bytes [a, b) (buffer offsets) to global memory: 16-byte rows, loose bytes at the ends.  One warp.
+__device__ __forceinline__ void df_flush(const DfShared& S, uint64_t a, uint64_t b, uint32_t lane) {
+    if (b > S.gcap) b = S.gcap;
+    if (b <= a) return;
+    uint64_t head = (16u - (uint32_t)((a + S.wlo) & 15u)) & 15u;
+    if (head > b - a) head = b - a;
+    if (lane < head) S.gdst[a + lane] = S.wdata[df_widx(S, (int64_t)(a + lane))];
+    a += head;
+    const uint64_t nq = (b - a) >> 4;
+    for (uint64_t q = lane; q < nq; q += 32u)
+        *(uint4*)(S.gdst + a + 16u * q) = *(const uint4*)(S.wdata + df_widx(S, (int64_t)(a + 16u * q)));
+    a += nq << 4;
+    if (lane < b - a) S.gdst[a + lane] = S.wdata[df_widx(S, (int64_t)(a + lane))];
 }
 
 // Per-lane byte copy of n bytes; loads are batched four at a time ahead of the stores so that a lane
@@ -569,14 +590,22 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
         // ---- literals: lane i copies the literals of sequence i; long runs use the whole warp
         {
             const bool act = lane < n && my_ll != 0;
-            if (act && my_ll <= LANE_CAP) lane_copy(dp + my_op, sp + my_lit, my_ll);
+            const bool wmode = DF && B2_DF_SMEMWIN && !solo;                 // the bytes go to the CTA's data window, not to global memory
+            if (act && my_ll <= LANE_CAP) {
+                if (wmode) {
+                    const uint32_t di = df_widx(c.df, abs0 + my_op);
+                    if (di + my_ll <= DF_DATA_BYTES) lane_copy(c.df.wdata + di, sp + my_lit, my_ll);
+                    else for (uint32_t k = 0; k < my_ll; ++k) c.df.wdata[(di + k) & DF_DATA_MASK] = sp[my_lit + k];
+                } else lane_copy(dp + my_op, sp + my_lit, my_ll);
+            }
             uint32_t longm = __ballot_sync(FULL_MASK, act && my_ll > LANE_CAP);
             const uint32_t longm0 = longm;
             while (longm) {
                 const int j = __ffs(longm) - 1; longm &= longm - 1;
                 const uint32_t l = __shfl_sync(FULL_MASK, my_lit, j), o = __shfl_sync(FULL_MASK, my_op, j);
                 const uint32_t len = __shfl_sync(FULL_MASK, my_ll, j);
-                group_copy_small(dp + o, sp + l, len, lane, 32);
+                if (wmode) { const uint32_t di = df_widx(c.df, abs0 + o); for (uint32_t i = lane; i < len; i += 32u) c.df.wdata[(di + i) & DF_DATA_MASK] = sp[l + i]; }
+                else group_copy_small(dp + o, sp + l, len, lane, 32);
             }
             if (DF && !solo) {                                              // literals never wait: publish them at once
                 DF_FENCE();
@@ -665,7 +694,19 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 const bool ready = mine && my_span <= 256u && df_ready(c.df, xa, xb);
                 if (ready && small) {
                     DF_FENCE();
-#if B2_DF_PIPECOPY
+#if B2_DF_SMEMWIN
+                    {   // destination in the data window; the source there too unless it is older than the window holds (or history)
+                        const DfShared& S = c.df; const int64_t slo = c.df_slo;
+                        const uint32_t di = df_widx(S, abs0 + my_mop), si = df_widx(S, xa);
+                        const bool in_w = xa >= slo;
+                        const bool simple = my_off >= my_ml && di + my_ml <= DF_DATA_BYTES && (in_w ? si + my_ml <= DF_DATA_BYTES : xb <= slo);
+                        if (simple) lane_copy(S.wdata + di, in_w ? (const uint8_t*)(S.wdata + si) : (const uint8_t*)(S.gdst + xa), my_ml);
+                        else {
+                            uint32_t r = 0;
+                            for (uint32_t k = 0; k < my_ml; ++k) { S.wdata[(di + k) & DF_DATA_MASK] = df_getb(S, slo, xa + r); r = (r + 1u == my_off) ? 0u : r + 1u; }
+                        }
+                    }
+#elif B2_DF_PIPECOPY
                     lane_copy_pipelined(dp + my_mop, my_src, my_ml, my_off >= my_ml ? 0u : my_off);
 #else
                     if (my_off >= my_ml) lane_copy(dp + my_mop, my_src, my_ml); else lane_match_from(dp + my_mop, my_src, my_off, my_ml);
@@ -688,13 +729,27 @@ __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
                 while (lb) {                                                // long matches: the whole warp copies
                     const int g = __ffs(lb) - 1; lb &= lb - 1;
                     const uint32_t W = __shfl_sync(FULL_MASK, my_mop, g), ml_g = __shfl_sync(FULL_MASK, my_ml, g), off_g = __shfl_sync(FULL_MASK, my_off, g);
-                    const uint8_t* m = dp + (__shfl_sync(FULL_MASK, xa, g) - abs0);
+                    const int64_t xa_g = __shfl_sync(FULL_MASK, xa, g);
+                    const uint8_t* m = dp + (xa_g - abs0);
                     DF_FENCE();
+#if B2_DF_SMEMWIN
+                    {
+                        const DfShared& S = c.df; const int64_t slo = c.df_slo;
+                        const uint32_t di = df_widx(S, abs0 + W);
+                        if (off_g >= ml_g) { for (uint32_t i = lane; i < ml_g; i += 32u) S.wdata[(di + i) & DF_DATA_MASK] = df_getb(S, slo, xa_g + i); }
+                        else {
+                            uint32_t r = lane % off_g; const uint32_t step = 32u % off_g;
+                            for (uint32_t i = lane; i < ml_g; i += 32u) { S.wdata[(di + i) & DF_DATA_MASK] = df_getb(S, slo, xa_g + r); r += step; if (r >= off_g) r -= off_g; }
+                        }
+                        (void)m;
+                    }
+#else
                     if (off_g >= ml_g) group_copy_small(dp + W, m, ml_g, lane, 32);
                     else {                                                  // overlapping: period replication from the final window
                         uint32_t r = lane % off_g; const uint32_t step = 32u % off_g;
                         for (uint32_t i = lane; i < ml_g; i += 32) { dp[W + i] = m[r]; r += step; if (r >= off_g) r -= off_g; }
                     }
+#endif
                     DF_FENCE();
                     __syncwarp();
                     df_mark_warp(c.df, (uint64_t)(abs0 + W), (uint64_t)(abs0 + W) + ml_g, lane);

@@ -71,9 +71,20 @@ constexpr uint32_t DF_G = 1024u;            // compressed bytes per group = one 
 constexpr uint32_t DF_LA = 96u;             // bytes behind a group its parse may look at (length runs longer than that: DF_SLOW)
 constexpr uint32_t DF_RUN = 64u;            // 255-bytes of one length field followed inside the table pass
 constexpr uint32_t DF_BATCH = 32u;          // sequences per ticket (one per lane of the warp that decodes it)
+// B2_DF_SMEMWIN: the unit's most recent output lives in a circular DATA window in shared memory next to the bitmap; every byte
+// is written there, a match reads its source there (a shared-memory round trip instead of one through L2 per link of the
+// dependency chain), and the warp that retires a ticket writes its bytes to global memory in 16-byte rows.
+#ifndef B2_DF_SMEMWIN
+#define B2_DF_SMEMWIN 0
+#endif
+#if B2_DF_SMEMWIN
+constexpr uint32_t DF_WIN_BYTES = 128u << 10;   // output window covered by the bitmap (16 KB of shared memory) and by the data window (128 KB)
+#else
 constexpr uint32_t DF_WIN_BYTES = 512u << 10;   // output window covered by the CTA's "final bytes" bitmap (64 KB of shared memory)
+#endif
 constexpr uint32_t DF_WIN_MASK = DF_WIN_BYTES / 32u - 1u;
 constexpr uint32_t DF_HALF = DF_WIN_BYTES / 2u; // a ticket is handed out when its output ends within this much of the watermark
+constexpr uint32_t DF_DATA_BYTES = B2_DF_SMEMWIN ? DF_WIN_BYTES : 0u, DF_DATA_MASK = DF_DATA_BYTES ? DF_DATA_BYTES - 1u : 0u;
 #ifndef B2_DF_NAP_MIN
 #define B2_DF_NAP_MIN 64
 #endif
@@ -86,6 +97,10 @@ struct DfHead { uint32_t exit, out; };      // chain from one position of a grou
 struct DfShared {                           // per-CTA dataflow state in shared memory (decode_df_kernel)
     uint32_t* bits;                         // DF_WIN_BYTES / 32 words, circular: bit of output byte p is (p mod DF_WIN_BYTES)
     volatile unsigned long long* final_below;   // every output byte below this buffer offset is final
+    uint8_t* wdata;                         // B2_DF_SMEMWIN: DF_DATA_BYTES of shared memory, byte of buffer offset p at (p + wlo) mod DF_DATA_BYTES
+    uint8_t* gdst;                          // ... the destination buffer (buffer offset 0)
+    uint32_t wlo;                           // ... low 4 bits of gdst (16-byte rows of the window are 16-byte rows of global memory)
+    uint64_t gcap;                          // ... its capacity (nothing is flushed beyond it)
 };
 struct DfState {
     unsigned long long bad_key;             // min over failures of (block << 8 | Err); all ones = none

@@ -449,6 +449,7 @@ static uint32_t df_mode() { return df_level() == 0 ? 0u : df_level() == 2 ? (SCA
 static uint32_t df_cta_warps(const b2lz4_ctx* ctx, size_t n, size_t cap) {
     static int env = -1;
     if (env < 0) { const char* e = getenv("B2LZ4_DF_WARPS"); env = e ? atoi(e) : 0; }
+    if (B2_DF_SMEMWIN) return 32u;                 // the data window leaves room for one CTA per SM only
     if (env == 8 || env == 16 || env == 32) return (uint32_t)env;
     (void)n;
     return cap >= ((size_t)2 * ctx->sm_count << 22) ? 16u : 32u;      // >= two 4 MB blocks per SM: many units
