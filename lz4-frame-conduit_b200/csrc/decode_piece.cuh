@@ -150,8 +150,17 @@ __device__ __forceinline__ void df_flush(const DfShared& S, uint64_t a, uint64_t
 
 // Per-lane byte copy of n bytes; loads are batched four at a time ahead of the stores so that a lane
 // keeps several loads in flight.  `s` must not overlap the destination (callers guarantee it).
+#ifndef B2_LANE_COPY8
+#define B2_LANE_COPY8 0       // 1 = eight loads in flight before the first store (half the dependent round trips of a long copy, same instruction count)
+#endif
 __device__ __forceinline__ void lane_copy(uint8_t* d, const uint8_t* s, uint32_t n) {
     uint32_t k = 0;
+#if B2_LANE_COPY8
+    for (; k + 8 <= n; k += 8) {
+        uint8_t a = s[k], b = s[k + 1], c = s[k + 2], e = s[k + 3], f = s[k + 4], g = s[k + 5], h = s[k + 6], i = s[k + 7];
+        d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e; d[k + 4] = f; d[k + 5] = g; d[k + 6] = h; d[k + 7] = i;
+    }
+#endif
     for (; k + 4 <= n; k += 4) {
         uint8_t a = s[k], b = s[k + 1], c = s[k + 2], e = s[k + 3];
         d[k] = a; d[k + 1] = b; d[k + 2] = c; d[k + 3] = e;
