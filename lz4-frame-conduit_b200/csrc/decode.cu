@@ -265,13 +265,23 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
                 ncb == 0 || fc != cnt || (uint64_t)fc + ncb > nc || ((w >> 31) && (ncb != 1 || cs != us))) { s_bad = 1; break; }
             BlockRef br; br.src_off = a + 4; br.csize = cs; br.stored = w >> 31; br.dst_off = d; br.usize = us; br.pad = 0;
             blocks[b] = br;
-            bool bad = false;                                       // (no exit from inside the loop: the loads of the next entries do not wait for this one's checks)
-            #pragma unroll 4
-            for (uint32_t k = 0; k < ncb; ++k) {
-                const uint8_t* ce = ic + (uint64_t)(fc + k) * sizeof(IndexChain);
-                uint32_t tok = ld_le32_dev(ce), out = ld_le32_dev(ce + 4);
-                uint32_t tok_n = cs, out_n = us;
-                if (k + 1 < ncb) { tok_n = ld_le32_dev(ce + 8); out_n = ld_le32_dev(ce + 12); }
+            bool bad = false;                                       // (no exit from inside the loop: a bad entry is reported behind it)
+            // the entries are read eight at a time, all loads first: one memory round trip per eight entries instead of one each
+            // (this kernel is one CTA in front of the decoder: 126 K cycles for 27 K instructions before)
+            constexpr uint32_t EB = 8;
+            uint32_t etok[EB + 1], eout[EB + 1];
+            for (uint32_t k0 = 0; k0 < ncb; k0 += EB) {
+              #pragma unroll
+              for (uint32_t j = 0; j <= EB; ++j) {
+                  const uint32_t k = k0 + j;
+                  const uint8_t* ce = ic + (uint64_t)(fc + k) * sizeof(IndexChain);
+                  etok[j] = k < ncb ? ld_le32_dev(ce) : cs; eout[j] = k < ncb ? ld_le32_dev(ce + 4) : us;
+              }
+              #pragma unroll
+              for (uint32_t j = 0; j < EB; ++j) {
+                const uint32_t k = k0 + j;
+                if (k >= ncb) break;
+                const uint32_t tok = etok[j], out = eout[j], tok_n = etok[j + 1], out_n = eout[j + 1];
                 if ((k == 0 && (tok != 0 || out != 0)) || tok >= tok_n || out > out_n || tok_n > cs || out_n > us) { bad = true; continue; }
                 Piece pc; pc.src_off = a + 4 + tok; pc.src_len = tok_n - tok;
                 pc.flags = PIECE_EXACT | (br.stored ? (PIECE_STORED | PIECE_BULK) : 0u) | (k + 1 == ncb ? PIECE_ENDS_BLOCK : 0u);
@@ -280,6 +290,7 @@ frame_scan_kernel(const uint8_t* __restrict__ src, uint64_t n, uint64_t dst_cap,
                 pieces[fc + k] = pc;
                 Chain ch; ch.dst_off = d + out; ch.first_piece = fc + k; ch.n_pieces = 1;
                 chains[fc + k] = ch;
+              }
             }
             if (bad) { s_bad = 1; break; }
             a += 4ull + cs + bc; d += us; cnt += ncb;
@@ -529,10 +540,16 @@ decode_finalize_kernel(const FrameIndex* __restrict__ fi, const Piece* __restric
     }
     const uint32_t np = fi->n_pieces, nb = fi->n_blocks, bs = fi->block_size;
     unsigned long long tot = 0;
-    for (uint32_t i = tid; i < np; i += blockDim.x) {
-        PieceOut po = outs[i];
-        if (po.err) atomicMin(&s_first_bad, i);
-        tot += po.out_len;
+    for (uint32_t i0 = tid; i0 < np; i0 += 8u * blockDim.x) {       // eight loads in flight per thread (one CTA: latency is all there is)
+        PieceOut po[8];
+        #pragma unroll
+        for (uint32_t j = 0; j < 8u; ++j) { const uint32_t i = i0 + j * blockDim.x; po[j] = i < np ? outs[i] : PieceOut{0, 0}; }
+        #pragma unroll
+        for (uint32_t j = 0; j < 8u; ++j) {
+            const uint32_t i = i0 + j * blockDim.x;
+            if (i < np && po[j].err) atomicMin(&s_first_bad, i);
+            tot += po[j].out_len;
+        }
     }
     // a non-final block that decodes short breaks the "block b starts at b*block_size" layout
     if (!fi->layout_known && fi->n_chains == nb) {
