@@ -259,6 +259,42 @@ def test_emu_dataflow_forced_for_every_frame(emu):
     assert "ok" in _run_with_env({"B2LZ4_DF": "0"}, _GOLDEN_LOOP)          # and everything without them
 
 
+_STREAM_LOOP = """
+import ctypes as C, os, random, subprocess, sys
+lib = C.CDLL(os.environ['B2LZ4_LIB']); sz = C.c_size_t
+lib.LZ4F_createDecompressionContext.argtypes = [C.POINTER(C.c_void_p), C.c_uint]; lib.LZ4F_createDecompressionContext.restype = sz
+lib.LZ4F_freeDecompressionContext.argtypes = [C.c_void_p]; lib.LZ4F_freeDecompressionContext.restype = sz
+lib.LZ4F_decompress.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(sz), C.c_void_p, C.POINTER(sz), C.c_void_p]; lib.LZ4F_decompress.restype = sz
+lib.LZ4F_isError.argtypes = [sz]; lib.LZ4F_getErrorName.argtypes = [sz]; lib.LZ4F_getErrorName.restype = C.c_char_p
+gen = C.CDLL('tools/libb2gen.so'); gen.b2gen_loglike.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64]
+b = C.create_string_buffer(9 << 20); gen.b2gen_loglike(b, 9 << 20, 21)
+d = b.raw + os.urandom(300000) + bytes(1 << 20)
+rnd = random.Random(4)
+for flags in (['-B4'], ['-B4', '-BD'], ['-B6', '-BX'], ['-B7', '--no-frame-crc']):
+    fr = subprocess.run(['oracle/_ref/lz4', '-c', *flags], input=d, capture_output=True, check=True).stdout
+    for srcmax, dstmax in ((65536, 65536), (1 << 20, 9000), (3000, 2 << 20)):
+        ctx = C.c_void_p(); assert lib.LZ4F_createDecompressionContext(C.byref(ctx), 100) == 0
+        out = bytearray(); pos = 0; dst = C.create_string_buffer(dstmax); src = C.create_string_buffer(fr, len(fr))
+        while True:
+            take = min(len(fr) - pos, rnd.randint(1, srcmax)); s = sz(take); o = sz(rnd.randint(0 if take else 1, dstmax))
+            h = lib.LZ4F_decompress(ctx, dst, C.byref(o), C.addressof(src) + pos, C.byref(s), None)
+            assert not lib.LZ4F_isError(h), lib.LZ4F_getErrorName(h)
+            out += dst.raw[:o.value]; pos += s.value
+            if h == 0: break
+        lib.LZ4F_freeDecompressionContext(ctx)
+        assert bytes(out) == d and pos == len(fr), (flags, srcmax, dstmax, len(out), pos)
+print('ok')
+"""
+
+
+def test_emu_streaming_decode_several_batches_random_slices(emu, lz4_cli):
+    """LZ4F_decompress (lz4frame.c:1380-1840 contract) over stock-CLI frames that take several GPU batches (B2LZ4_BATCH_MB=4), fed
+    and drained in random slices: the layer stages and launches the next batch while the caller still drains the one before."""
+    if lz4_cli is None:
+        pytest.skip("oracle/_ref/lz4 not present")
+    assert "ok" in _run_with_env({"B2LZ4_BATCH_MB": "4"}, _STREAM_LOOP)
+
+
 def test_emu_lane_order_does_not_matter(emu):
     """The lanes of a warp run in reverse / shuffled order between collectives: a missing __syncwarp() shows as a wrong byte."""
     for order in ("reverse", "random"):
