@@ -13,7 +13,7 @@ def loglike(n):
 ref=conftest._bind_replay(C.CDLL(os.path.join(ROOT,"oracle/_ref/libref.so")))
 data={"loglike":loglike(n<<20), "datagen":subprocess.run([os.path.join(ROOT,"oracle/_ref/datagen"),f"-g{n<<20}","-s1"],capture_output=True,check=True).stdout}
 with mod.Codec(0) as c:
-    c.set_prefs(block_size_id=7, sub_block_log2=17, write_index=0)
+    c.set_prefs(block_size_id=7, sub_block_log2=int(os.environ.get("SUB_LOG2","17")), write_index=0)
     for name,d in data.items():
         cap=len(d)+len(d)//100+100000; o=C.create_string_buffer(cap)
         r=ref.ref_conduit_compress(d,len(d),o,cap,0,0)
