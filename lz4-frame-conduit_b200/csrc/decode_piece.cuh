@@ -302,6 +302,9 @@ constexpr uint32_t WSTOP = 255u;       // link-table value: the token here needs
 #define B2_DEC_LANE_CAP 24
 #endif
 constexpr uint32_t LANE_CAP = B2_DEC_LANE_CAP;      // copies up to this many bytes run one-lane-per-sequence; longer ones use the whole warp
+#ifndef B2_DF_LANE_CAP
+#define B2_DF_LANE_CAP 16     // ... in the dataflow kernel, whose rounds run with few lanes each: a shorter per-lane loop pays (measured: 16 is
+#endif                        // 4 % faster than 24 there and 6 % slower in the one-warp-per-piece kernel, profiles/r3l_lane_copy_variants.txt)
 
 // Decodes one piece.  The warp first WALKS up to 32 sequences (uniform control flow: every lane follows the
 // token chain, lane i keeps the fields of sequence i), then copies them lane-parallel: literals of all 32
@@ -313,6 +316,7 @@ constexpr uint32_t LANE_CAP = B2_DEC_LANE_CAP;      // copies up to this many by
 template <bool DF>
 __device__ B2_NOINLINE uint32_t decode_piece(Cursor& c, bool ends_block)
 {
+    constexpr uint32_t LANE_CAP = DF ? (uint32_t)B2_DF_LANE_CAP : b2::LANE_CAP;   // (shadows the namespace-scope value)
     const uint32_t lane = lane_id();
     const uint8_t* __restrict__ sp = c.sp;
     uint8_t* dp = c.dp;
