@@ -259,6 +259,28 @@ def test_emu_dataflow_forced_for_every_frame(emu):
     assert "ok" in _run_with_env({"B2LZ4_DF": "0"}, _GOLDEN_LOOP)          # and everything without them
 
 
+def test_emu_static_scratch_checksums(emu, oracle, gen):
+    """b2lz4_xxh32_ranges_static on the emulator (the GPU test is tests/test_zz_no_alloc.py): hashes equal the oracle's, two calls in
+    a row share the scratch array, the limit and out-of-buffer ranges are refused with the documented error."""
+    lib = emu.load()
+    data = gen_bytes(gen, "loglike", 300000) + bytes(5000) + gen_bytes(gen, "random", 60000, 3)
+    buf = C.create_string_buffer(data, len(data))
+    rnd = random.Random(9)
+    for n in (400, 150):
+        offs = [rnd.randrange(0, len(data) - 9000) for _ in range(n)]
+        lens = [rnd.choice((0, 1, 15, 16, 17, 255, 4096, 8999)) for _ in range(n)]
+        a = (C.c_uint64 * n)(*offs); b = (C.c_uint32 * n)(*lens); out = (C.c_uint32 * n)()
+        r = lib.b2lz4_xxh32_ranges_static(0, None, C.addressof(buf), len(data), a, b, n, out)
+        assert not lib.b2lz4_is_error(r), lib.b2lz4_static_last_error()
+        for i in range(n):
+            assert out[i] == oracle.orc_xxh32(data[offs[i]:offs[i] + lens[i]], lens[i], 0), (n, i)
+    big = 65537
+    r = lib.b2lz4_xxh32_ranges_static(0, None, C.addressof(buf), len(data), (C.c_uint64 * big)(), (C.c_uint32 * big)(), big, (C.c_uint32 * big)())
+    assert lib.b2lz4_is_error(r) and lib.b2lz4_error_name(r) == b"ERROR_srcSize_tooLarge" and b"B2LZ4_STATIC_MAX_RANGES" in lib.b2lz4_static_last_error()
+    r = lib.b2lz4_xxh32_ranges_static(0, None, C.addressof(buf), len(data), (C.c_uint64 * 1)(len(data) - 3), (C.c_uint32 * 1)(4), 1, (C.c_uint32 * 1)())
+    assert lib.b2lz4_is_error(r) and b"leaves the buffer" in lib.b2lz4_static_last_error()
+
+
 _STREAM_LOOP = """
 import ctypes as C, os, random, subprocess, sys
 lib = C.CDLL(os.environ['B2LZ4_LIB']); sz = C.c_size_t
